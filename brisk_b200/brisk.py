@@ -1,0 +1,209 @@
+"""Host-side mirror of the reference interface for the insertion path.
+
+Reference                                             here
+  Parameters(k, m, b)      brisk/parameters.hpp:24      Parameters(k, m, b)
+  Brisk<DATA>(params)      brisk/Brisk.hpp:47           Brisk(params, data_size=1, ...)
+  count_sequence           apps/counter.cpp:231         Brisk.count_reads(bases, offsets)
+  insert_superkmer         brisk/Brisk.hpp:123          Brisk.insert_reads / insert_kmers  (batched)
+  get_superkmer / get      brisk/Brisk.hpp:102 / :64    Brisk.get_reads / get_kmers        (batched)
+  next / restart           brisk/Brisk.hpp:166-179      Brisk.dump()
+  stats                    brisk/Brisk.hpp:194          Brisk.stats()
+  SuperKmerEnumerator      brisk/Kmers.cpp:509-603      Brisk.enumerate_reads + decode_records
+
+Arrays are numpy arrays on the host or anything exposing a CUDA pointer through `.data_ptr()`
+(torch tensors) — pointers are handed to the C ABI untouched.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+KMER_DT = np.dtype([("lo", "<u8"), ("hi", "<u8"), ("idx", "u1"), ("pad", "u1", (7,))])
+NO_SLOT = np.uint64(0xFFFFFFFFFFFFFFFF)
+F_MANAGED = 1
+F_LITERAL_DECYCLE = 2
+
+
+class BriskError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _capi.LIB_PATH
+
+
+class Parameters:
+    """Parameters(k, m, b) — brisk/parameters.hpp:24-34 (derived constants included)."""
+
+    def __init__(self, k, m, b):
+        self.k, self.m, self.b = int(k), int(m), int(b)
+        self.m_reduc = self.m - self.b
+        self.compacted_size = self.k - self.b
+        self.allocated_bytes = (2 * self.k - self.m - self.b + 3) // 4
+        self.mask_large_minimizer = (1 << (2 * self.m)) - 1
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if hasattr(a, "data_ptr"):
+        return C.c_void_p(a.data_ptr())
+    if isinstance(a, (bytes, bytearray)):
+        return C.cast(C.c_char_p(bytes(a)), C.c_void_p)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Brisk:
+    """Brisk<DATA> over libbrisk_b200.so.  data_size = sizeof(DATA) (1 = the counter's uint8_t)."""
+
+    def __init__(self, params, data_size=1, device=-1, capacity_hint=0, flags=0):
+        if not isinstance(params, Parameters):
+            params = Parameters(*params)
+        self.params = params
+        self.data_size = data_size
+        self._lib = _capi.load()
+        h = C.c_void_p()
+        rc = self._lib.brisk_create(params.k, params.m, params.b, data_size, device, capacity_hint, flags, C.byref(h))
+        self._h = h if rc == 0 else None
+        self._check(rc)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise BriskError("brisk_b200 error %d: %s" % (rc, self._lib.brisk_last_error().decode()))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.brisk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- reads
+    @staticmethod
+    def _n_reads(offsets):
+        return (offsets.numel() if hasattr(offsets, "numel") else len(offsets)) - 1
+
+    def enumerate_reads(self, bases, offsets):
+        """(records[n, rec_words] uint64, rec_words) — one packed record per emitted superkmer."""
+        n = self._n_reads(offsets)
+        cnt, rw = C.c_uint64(), C.c_uint32()
+        self._check(self._lib.brisk_enumerate_reads(self._h, _ptr(bases), _ptr(offsets), n, None, 0, C.byref(cnt), C.byref(rw)))
+        recs = np.zeros((cnt.value, rw.value), np.uint64)
+        if cnt.value:
+            self._check(self._lib.brisk_enumerate_reads(self._h, _ptr(bases), _ptr(offsets), n, _ptr(recs), cnt.value,
+                                                        C.byref(cnt), C.byref(rw)))
+        return recs, rw.value
+
+    def count_reads(self, bases, offsets):
+        self._check(self._lib.brisk_count_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets)))
+
+    def n_occurrences(self, offsets):
+        lens = np.diff(np.asarray(offsets).astype(np.int64))
+        return int(np.maximum(lens - self.params.k + 1, 0).sum())
+
+    def insert_reads(self, bases, offsets):
+        """(slots, newly) per k-mer occurrence in read order."""
+        n_occ = self.n_occurrences(offsets)
+        slots = np.zeros(n_occ, np.uint64)
+        newly = np.zeros(n_occ, np.uint8)
+        self._check(self._lib.brisk_insert_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), _ptr(slots), _ptr(newly)))
+        return slots, newly
+
+    def get_reads(self, bases, offsets):
+        """(found, data) per k-mer occurrence in read order."""
+        n_occ = self.n_occurrences(offsets)
+        found = np.zeros(n_occ, np.uint8)
+        data = np.zeros((n_occ, self.data_size), np.uint8)
+        self._check(self._lib.brisk_get_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), _ptr(found), _ptr(data)))
+        return found, (data[:, 0] if self.data_size == 1 else data)
+
+    # ---- explicit k-mers
+    @staticmethod
+    def pack_kmers(lo, hi, idx):
+        k = np.zeros(len(lo), KMER_DT)
+        k["lo"], k["hi"], k["idx"] = lo, hi, idx
+        return k
+
+    def insert_kmers(self, kmers, count=False):
+        slots = np.zeros(len(kmers), np.uint64)
+        newly = np.zeros(len(kmers), np.uint8)
+        self._check(self._lib.brisk_insert_kmers(self._h, _ptr(kmers), len(kmers), _ptr(slots), _ptr(newly), int(count)))
+        return slots, newly
+
+    def get_kmers(self, kmers):
+        slots = np.zeros(len(kmers), np.uint64)
+        data = np.zeros((len(kmers), self.data_size), np.uint8)
+        self._check(self._lib.brisk_get_kmers(self._h, _ptr(kmers), len(kmers), _ptr(slots), _ptr(data)))
+        return slots, (data[:, 0] if self.data_size == 1 else data)
+
+    def data_ptr(self, slot):
+        return self._lib.brisk_data_ptr(self._h, int(slot))
+
+    # ---- whole index
+    def dump(self):
+        """(lo, hi, idx, data) of every stored k-mer, unordered."""
+        n = C.c_uint64()
+        self._check(self._lib.brisk_dump(self._h, None, None, 0, C.byref(n)))
+        keys = np.zeros(n.value, KMER_DT)
+        data = np.zeros((n.value, self.data_size), np.uint8)
+        if n.value:
+            self._check(self._lib.brisk_dump(self._h, _ptr(keys), _ptr(data), n.value, C.byref(n)))
+        return keys["lo"].copy(), keys["hi"].copy(), keys["idx"].copy(), (data[:, 0] if self.data_size == 1 else data)
+
+    def stats(self):
+        v = [C.c_uint64() for _ in range(5)]
+        self._check(self._lib.brisk_stats(self._h, *[C.byref(x) for x in v]))
+        names = ("nb_buckets", "nb_skmers", "nb_kmers", "memory_usage", "largest_bucket")
+        return {n: x.value for n, x in zip(names, v)}
+
+    def reserve(self, n_keys):
+        self._check(self._lib.brisk_reserve(self._h, n_keys))
+
+    def capacity(self):
+        c = C.c_uint64()
+        self._check(self._lib.brisk_capacity(self._h, C.byref(c)))
+        return c.value
+
+    def sync(self):
+        self._check(self._lib.brisk_sync(self._h))
+
+    def last_timing(self):
+        ms = (C.c_float * 5)()
+        n = C.c_uint32()
+        self._check(self._lib.brisk_last_timing(self._h, ms, C.byref(n)))
+        return dict(pack_ms=ms[0], enumerate_ms=ms[1], partition_ms=ms[2], store_ms=ms[3], total_ms=ms[4], launches=n.value)
+
+
+def decode_records(recs, params):
+    """Unpacks superkmer records (layout in DESIGN.md / csrc/common.cuh) into per-superkmer lists of
+    (kmer_s as int, minimizer_idx), in the reference's emission order, plus the bucket id.  Host-side
+    helper for tests and tools; pure bit unpacking, no algorithm."""
+    k, m, b = params.k, params.m, params.b
+    w = k - m + 1
+    wb = 1
+    while (1 << wb) < w:
+        wb += 1
+    rw = recs.shape[1]
+    sb = 64 - 2 * b
+    hb = 2 * b + 2 * wb
+    out = []
+    kmask = (1 << (2 * k)) - 1
+    for row in recs:
+        top = int(row[rw - 1])
+        bucket = top >> sb
+        n = ((top >> (sb - wb)) & ((1 << wb) - 1)) + 1
+        idx0 = (top >> (sb - 2 * wb)) & ((1 << wb) - 1)
+        val = 0
+        for i in range(rw - 1, -1, -1):
+            word = int(row[i])
+            if i == rw - 1:
+                word &= (1 << (64 - hb)) - 1
+            val = (val << 64) | word
+        kmers = [((val >> (2 * (n - 1 - j))) & kmask, idx0 + j) for j in range(n)]
+        out.append((bucket, kmers))
+    return out

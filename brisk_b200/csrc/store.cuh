@@ -1,0 +1,446 @@
+// store.cuh — the GPU-resident bucket store (north-star item 6).
+//
+// Replaces DenseMenuYo + Bucket + SKL (brisk/DenseMenuYo.hpp:248-396, brisk/buckets.hpp:146-225,
+// brisk/SuperKmerLight.hpp:209-217).  In the reference a k-mer is found by (bucket id, compacted
+// k-b nucleotides, position idx+s); that triple is a bijection of (kmer_s, minimizer_idx), so the store
+// is one open-addressing table keyed on (kmer_s, minimizer_idx):
+//
+//   KW = 1 (2k <= 64):  16-byte slot  { u64 key;      u32 meta; u32 aux;          }   two per 32-B sector
+//   KW = 2           :  32-byte slot  { u64 lo, hi;   u32 meta; u32 aux; u64 aux2 }   one per sector
+//   meta = (minimizer_idx + 1) in bits 0..7 (0 = claimed but not yet published), DATA byte (the
+//          counter's uint8_t) in bits 24..31 so that the wrapping ++ is a single atomicAdd(1<<24).
+//
+// insert = CAS-claim of the key word(s) (atomicCAS / atom.cas.b128), then one atomicAdd publishes the
+// idx tag and applies the first count.  A slot never moves until the table is rehashed, so the slot
+// index is the stable DATA handle that replaces the reference's realloc + protect_data.
+#pragma once
+#include "common.cuh"
+
+#define STORE_EMPTY (~0ull)
+#define STORE_MAX_PROBE 8192u
+#define META_TAG_MASK 0xFFu
+#define META_COUNT_ONE (1u << 24)
+
+struct Slot1 { u64 key; u32 meta; u32 aux; };
+struct Slot2 { u64 lo, hi; u32 meta; u32 aux; u64 aux2; };
+
+struct StoreView {
+    void *slots;        // Slot1[cap] or Slot2[cap]
+    u64 mask;           // cap - 1
+    u32 *special;       // [64] meta words of the one key that equals the empty pattern (poly-G at k = 32 / 64)
+    u64 *counters;      // [0] stored k-mers, [1] failed inserts, [2] records whose first k-mer was new, [3] dump cursor
+    u32 *bucket_bits;   // 4^b bits: bucket ids in use (null = not tracked)
+    unsigned char *data;  // DATA arena for data_size > 1 (null otherwise)
+    u32 data_size;
+    // failed inserts (probe limit hit) are parked here and replayed after a rehash
+    u64 *overflow;      // [ovf_cap][3]  lo, hi, idx | add<<8
+    u64 ovf_cap;
+};
+
+__device__ __forceinline__ u64 ld_cg64(const u64 *p) { return __ldcg(p); }
+__device__ __forceinline__ u32 ld_cg32(const u32 *p) { return __ldcg(p); }
+__device__ __forceinline__ void ld_relaxed128(const void *addr, u64 &lo, u64 &hi) {
+    asm volatile("{\n .reg .b128 d;\n ld.relaxed.gpu.global.b128 d, [%2];\n mov.b128 {%0,%1}, d;\n}\n"
+                 : "=l"(lo), "=l"(hi) : "l"(addr) : "memory");
+}
+__device__ __forceinline__ void cas128(void *addr, u64 clo, u64 chi, u64 slo, u64 shi, u64 &olo, u64 &ohi) {
+    asm volatile("{\n .reg .b128 c, s, d;\n mov.b128 c, {%3,%4};\n mov.b128 s, {%5,%6};\n"
+                 " atom.global.relaxed.gpu.cas.b128 d, [%2], c, s;\n mov.b128 {%0,%1}, d;\n}\n"
+                 : "=l"(olo), "=l"(ohi) : "l"(addr), "l"(clo), "l"(chi), "l"(slo), "l"(shi) : "memory");
+}
+
+template <int KW> struct SlotOf;
+template <> struct SlotOf<1> { typedef Slot1 type; };
+template <> struct SlotOf<2> { typedef Slot2 type; };
+
+template <int KW>
+__device__ __forceinline__ u32 *slot_meta_ptr(const StoreView &T, u64 slot) {
+    if (slot > T.mask) return T.special + (slot - T.mask - 1);
+    typedef typename SlotOf<KW>::type S;
+    return &reinterpret_cast<S *>(T.slots)[slot].meta;
+}
+
+// find-or-claim (kmer_s, idx).  add = increment applied to meta (META_COUNT_ONE for the counter, 0 for a
+// plain insert).  Returns 0 = found, 1 = newly inserted, -1 = probe limit reached (nothing changed).
+template <int KW>
+__device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 &slot_out) {
+    typedef typename SlotOf<KW>::type S;
+    const u32 tag = idx + 1;
+    if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
+        u32 old = atomicAdd(T.special + idx, add);
+        int res = 0;
+        if ((old & META_TAG_MASK) == 0) res = (atomicOr(T.special + idx, tag) & META_TAG_MASK) == 0 ? 1 : 0;
+        slot_out = T.mask + 1 + idx;
+        return res;
+    }
+    S *tab = reinterpret_cast<S *>(T.slots);
+    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
+    u32 probes = 0;
+    while (probes < STORE_MAX_PROBE) {
+        S *p = tab + s;
+        bool match;
+        if (KW == 1) {
+            u64 cur = ld_cg64(reinterpret_cast<const u64 *>(p));
+            if (cur == STORE_EMPTY) {
+                u64 old = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo);
+                if (old == STORE_EMPTY) {
+                    atomicAdd(&p->meta, tag | add);
+                    slot_out = s;
+                    return 1;
+                }
+                cur = old;
+            }
+            match = cur == lo;
+        } else {
+            u64 clo, chi;
+            ld_relaxed128(p, clo, chi);
+            if (clo == STORE_EMPTY && chi == STORE_EMPTY) {
+                u64 olo, ohi;
+                cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
+                if (olo == STORE_EMPTY && ohi == STORE_EMPTY) {
+                    atomicAdd(&p->meta, tag | add);
+                    slot_out = s;
+                    return 1;
+                }
+                clo = olo; chi = ohi;
+            }
+            match = clo == lo && chi == hi;
+        }
+        if (match) {
+            u32 t = ld_cg32(&p->meta) & META_TAG_MASK;
+            if (t == 0) continue;  // claimed by another thread, tag not published yet: look again
+            if (t == tag) {
+                if (add) atomicAdd(&p->meta, add);
+                slot_out = s;
+                return 0;
+            }
+        }
+        s = (s + 1) & T.mask;
+        probes++;
+    }
+    return -1;
+}
+
+// lookup only; returns true and the slot when present
+template <int KW>
+__device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 &slot_out, u32 &meta_out) {
+    typedef typename SlotOf<KW>::type S;
+    const u32 tag = idx + 1;
+    if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
+        u32 mt = ld_cg32(T.special + idx);
+        slot_out = T.mask + 1 + idx;
+        meta_out = mt;
+        return (mt & META_TAG_MASK) == tag;
+    }
+    const S *tab = reinterpret_cast<const S *>(T.slots);
+    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
+    for (u32 probes = 0; probes < STORE_MAX_PROBE;) {
+        const S *p = tab + s;
+        bool match;
+        if (KW == 1) {
+            u64 cur = ld_cg64(reinterpret_cast<const u64 *>(p));
+            if (cur == STORE_EMPTY) return false;
+            match = cur == lo;
+        } else {
+            u64 clo, chi;
+            ld_relaxed128(p, clo, chi);
+            if (clo == STORE_EMPTY && chi == STORE_EMPTY) return false;
+            match = clo == lo && chi == hi;
+        }
+        if (match) {
+            u32 mt = ld_cg32(&p->meta);
+            u32 t = mt & META_TAG_MASK;
+            if (t == 0) continue;
+            if (t == tag) { slot_out = s; meta_out = mt; return true; }
+        }
+        s = (s + 1) & T.mask;
+        probes++;
+    }
+    return false;
+}
+
+__device__ __forceinline__ void store_note_new(const StoreView &T, u64 bucket) {
+    if (T.bucket_bits) atomicOr(T.bucket_bits + (bucket >> 5), 1u << (bucket & 31));
+}
+__device__ __forceinline__ void store_park(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add) {
+    u64 i = atomicAdd(T.counters + 1, 1ull);
+    if (T.overflow && i < T.ovf_cap) {
+        T.overflow[3 * i] = lo; T.overflow[3 * i + 1] = hi; T.overflow[3 * i + 2] = (u64)idx | ((u64)add << 8);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k-mer j (emission order) of a record whose payload words are pw[] (header already masked off)
+template <int RW, int KW>
+__device__ __forceinline__ void record_kmer(const BriskParams &P, const u64 (&pw)[RW], int n, int j, u64 &lo, u64 &hi) {
+    int sh = 2 * (n - 1 - j);
+    lo = mw_extract64<RW>(pw, sh);
+    if (KW == 2) {
+        hi = mw_extract64<RW>(pw, sh + 64) & P.kmask_hi;
+    } else {
+        hi = 0;
+    }
+    lo &= P.kmask_lo;
+}
+
+enum { MODE_COUNT = 0, MODE_INSERT = 1, MODE_GET = 2 };
+
+struct OccOut {
+    const u64 *rec_occ;  // per record: (first read-order occurrence index << 1) | rev  (null: no per-occurrence output)
+    u64 *slots;          // per occurrence (nullable)
+    unsigned char *flags;  // per occurrence: newly (insert) / found (get) (nullable)
+    unsigned char *data;   // per occurrence data_size bytes (get, nullable)
+};
+
+// One warp takes 32 records at a time and spreads their k-mers over its lanes, so that every lane runs
+// one table operation per step whatever the superkmer sizes are.
+template <int RW, int KW, int MODE>
+__global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const u64 *__restrict__ recs, u64 n_recs,
+                                                      StoreView T, OccOut O) {
+    const int lane = threadIdx.x & 31;
+    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u64 n_warps = ((u64)gridDim.x * blockDim.x) >> 5;
+    const u64 top_mask = rec_payload_mask_top(P);
+    u32 new_keys = 0, new_recs = 0;
+    for (u64 r0 = warp * 32; r0 < n_recs; r0 += n_warps * 32) {
+        const u64 ri = r0 + lane;
+        u64 w[RW];
+        int n = 0, idx0 = 0;
+        u64 bucket = 0, occ = 0;
+        if (ri < n_recs) {
+            const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(recs + ri * RW);
+#pragma unroll
+            for (int i = 0; i < RW; i += 2) {
+                ulonglong2 v = __ldcs(src + (i >> 1));
+                w[i] = v.x; w[i + 1] = v.y;
+            }
+            rec_unpack_header(P, w[RW - 1], bucket, n, idx0);
+            w[RW - 1] &= top_mask;
+            if (O.rec_occ) occ = O.rec_occ[ri];
+        } else {
+#pragma unroll
+            for (int i = 0; i < RW; i++) w[i] = 0;
+        }
+        // inclusive prefix sum of n over the warp
+        int incl = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        for (int c = 0; c < total; c += 32) {
+            const int o = c + lane;
+            // source lane = number of lanes whose inclusive prefix is <= o
+            int src = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                int probe = __shfl_sync(0xffffffffu, incl, (src + step - 1) & 31);
+                if (src + step <= 32 && probe <= o) src += step;
+            }
+            const int src_l = src & 31;
+            const int s_incl = __shfl_sync(0xffffffffu, incl, src_l);
+            const int s_n = __shfl_sync(0xffffffffu, n, src_l);
+            const int s_idx0 = __shfl_sync(0xffffffffu, idx0, src_l);
+            const u64 s_bucket = __shfl_sync(0xffffffffu, bucket, src_l);
+            const u64 s_occ = __shfl_sync(0xffffffffu, occ, src_l);
+            u64 pw[RW];
+#pragma unroll
+            for (int i = 0; i < RW; i++) pw[i] = __shfl_sync(0xffffffffu, w[i], src_l);
+            if (o < total) {
+                const int j = o - (s_incl - s_n);
+                u64 lo, hi;
+                record_kmer<RW, KW>(P, pw, s_n, j, lo, hi);
+                const u32 idx = (u32)(s_idx0 + j);
+                u64 slot = ~0ull;
+                if (MODE == MODE_GET) {
+                    u32 mt = 0;
+                    bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
+                    if (O.rec_occ) {
+                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
+                        if (O.flags) O.flags[oi] = found;
+                        if (O.slots) O.slots[oi] = found ? slot : ~0ull;
+                        if (O.data) {
+                            if (T.data_size == 1) O.data[oi] = found ? (unsigned char)(mt >> 24) : 0;
+                            else for (u32 q = 0; q < T.data_size; q++)
+                                O.data[oi * T.data_size + q] = found ? T.data[slot * T.data_size + q] : 0;
+                        }
+                    }
+                } else {
+                    const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
+                    int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+                    if (res == 1) {
+                        new_keys++;
+                        if (j == 0) new_recs++;
+                        store_note_new(T, s_bucket);
+                    } else if (res < 0) {
+                        store_park(T, lo, hi, idx, add);
+                    }
+                    if (O.rec_occ) {
+                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
+                        if (O.flags) O.flags[oi] = res == 1;
+                        if (O.slots) O.slots[oi] = res < 0 ? ~0ull : slot;
+                    }
+                }
+            }
+        }
+    }
+    if (MODE != MODE_GET) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            new_keys += __shfl_xor_sync(0xffffffffu, new_keys, d);
+            new_recs += __shfl_xor_sync(0xffffffffu, new_recs, d);
+        }
+        if (lane == 0) {
+            if (new_keys) atomicAdd(T.counters + 0, (u64)new_keys);
+            if (new_recs) atomicAdd(T.counters + 2, (u64)new_recs);
+        }
+    }
+}
+
+// explicit k-mers: Brisk::insert / Brisk::get.  kmers = {lo, hi, idx, pad} as brisk_kmer (24 bytes).
+struct KmerIn { u64 lo, hi; unsigned char idx; unsigned char pad[7]; };
+
+template <int KW, int MODE>
+__global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const KmerIn *__restrict__ kmers, u64 n, StoreView T,
+                                                    u64 *slots, unsigned char *flags, unsigned char *data) {
+    u32 new_keys = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        {
+            u64 lo = kmers[i].lo & P.kmask_lo, hi = kmers[i].hi & P.kmask_hi;
+            u32 idx = kmers[i].idx;
+            u64 slot = ~0ull;
+            if (MODE == MODE_GET) {
+                u32 mt = 0;
+                bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
+                if (slots) slots[i] = found ? slot : ~0ull;
+                if (flags) flags[i] = found;
+                if (data) {
+                    if (T.data_size == 1) data[i] = found ? (unsigned char)(mt >> 24) : 0;
+                    else for (u32 q = 0; q < T.data_size; q++) data[i * T.data_size + q] = found ? T.data[slot * T.data_size + q] : 0;
+                }
+            } else {
+                const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
+                int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+                if (res == 1) {
+                    new_keys++;
+                    store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
+                } else if (res < 0) {
+                    store_park(T, lo, hi, idx, add);
+                }
+                if (slots) slots[i] = res < 0 ? ~0ull : slot;
+                if (flags) flags[i] = res == 1;
+            }
+        }
+    }
+    if (MODE != MODE_GET) {
+        // lanes may have left the loop at different times; plain per-thread atomics keep this simple
+        if (new_keys) atomicAdd(T.counters + 0, (u64)new_keys);
+    }
+}
+
+// replay of parked inserts after a rehash
+template <int KW>
+__global__ void __launch_bounds__(256) replay_kernel(const BriskParams P, const u64 *__restrict__ parked, u64 n, StoreView T) {
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        u64 lo = parked[3 * i], hi = parked[3 * i + 1], x = parked[3 * i + 2];
+        u32 idx = (u32)(x & 0xFF), add = (u32)(x >> 8);
+        u64 slot;
+        int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+        if (res == 1) {
+            atomicAdd(T.counters + 0, 1ull);
+            store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
+        } else if (res < 0) {
+            store_park(T, lo, hi, idx, add);
+        }
+    }
+}
+
+// rehash: every occupied slot of `from` is re-seated in `to` with its meta / aux / DATA
+template <int KW>
+__global__ void __launch_bounds__(256) rehash_kernel(StoreView from, StoreView to) {
+    typedef typename SlotOf<KW>::type S;
+    const S *src = reinterpret_cast<const S *>(from.slots);
+    S *dst = reinterpret_cast<S *>(to.slots);
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i <= from.mask; i += (u64)gridDim.x * blockDim.x) {
+        S v = src[i];
+        u64 lo = *reinterpret_cast<const u64 *>(&v);
+        u64 hi = KW == 2 ? reinterpret_cast<const u64 *>(&v)[1] : 0;
+        if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) continue;
+        u32 idx = (v.meta & META_TAG_MASK) - 1;
+        u64 s = slot_hash(lo, hi, idx) & to.mask;
+        for (;;) {
+            S *p = dst + s;
+            bool won;
+            if (KW == 1) {
+                won = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo) == STORE_EMPTY;
+            } else {
+                u64 olo, ohi;
+                cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
+                won = olo == STORE_EMPTY && ohi == STORE_EMPTY;
+            }
+            if (won) {
+                p->meta = v.meta;
+                p->aux = v.aux;
+                if (KW == 2) reinterpret_cast<u64 *>(p)[3] = reinterpret_cast<const u64 *>(&v)[3];
+                if (from.data) for (u32 q = 0; q < from.data_size; q++) to.data[s * to.data_size + q] = from.data[i * from.data_size + q];
+                break;
+            }
+            s = (s + 1) & to.mask;
+        }
+    }
+}
+
+// dump: compacts occupied slots into (key, data) arrays (unordered)
+template <int KW>
+__global__ void __launch_bounds__(256) dump_kernel(StoreView T, KmerIn *keys, unsigned char *data, u64 cap_out, int n_special) {
+    typedef typename SlotOf<KW>::type S;
+    const S *tab = reinterpret_cast<const S *>(T.slots);
+    const u64 total = T.mask + 1 + (u64)n_special;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x) {
+        u64 lo, hi = 0;
+        u32 meta;
+        if (i <= T.mask) {
+            lo = *reinterpret_cast<const u64 *>(tab + i);
+            if (KW == 2) hi = reinterpret_cast<const u64 *>(tab + i)[1];
+            if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) continue;
+            meta = tab[i].meta;
+        } else {
+            meta = T.special[i - T.mask - 1];
+            if ((meta & META_TAG_MASK) == 0) continue;
+            lo = STORE_EMPTY;
+            hi = KW == 2 ? STORE_EMPTY : 0;
+        }
+        u64 o = atomicAdd(T.counters + 3, 1ull);
+        if (o < cap_out) {
+            if (keys) {
+                KmerIn kk;
+                kk.lo = lo; kk.hi = hi; kk.idx = (unsigned char)((meta & META_TAG_MASK) - 1);
+                for (int q = 0; q < 7; q++) kk.pad[q] = 0;
+                keys[o] = kk;
+            }
+            if (data) {
+                if (T.data_size == 1) data[o] = (unsigned char)(meta >> 24);
+                else for (u32 q = 0; q < T.data_size; q++) data[o * T.data_size + q] = T.data[i * T.data_size + q];
+            }
+        }
+    }
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256) init_table_kernel(void *slots, u64 cap) {
+    // every 16 bytes: either an empty key (+ for KW = 2 the zero meta/aux half) or {EMPTY, 0}
+    ulonglong2 *p = reinterpret_cast<ulonglong2 *>(slots);
+    const u64 n16 = cap * (KW == 1 ? 1 : 2);
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (u64)gridDim.x * blockDim.x) {
+        if (KW == 1) p[i] = make_ulonglong2(STORE_EMPTY, 0ull);
+        else p[i] = (i & 1) ? make_ulonglong2(0ull, 0ull) : make_ulonglong2(STORE_EMPTY, STORE_EMPTY);
+    }
+}
+
+__global__ void __launch_bounds__(256) popcount_kernel(const u32 *bits, u64 n_words, u64 *out) {
+    u64 acc = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (u64)gridDim.x * blockDim.x) acc += __popc(bits[i]);
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}

@@ -1,0 +1,128 @@
+/*
+ * brisk_b200.h — C ABI of libbrisk_b200.so, the B200-native k-mer insertion path of Brisk.
+ *
+ * The reference has no FFI: its insertion path sits behind a header-only C++ template API
+ * (brisk/Brisk.hpp:23-42, brisk/Kmers.hpp:32-89, brisk/parameters.hpp:9-35) called by
+ * apps/counter.cpp.  This header is the boundary a binding would target; the C++ mirror of
+ * the reference API (include/brisk_b200/Brisk.hpp) and the Python host class
+ * (brisk_b200/brisk.py) are thin wrappers over exactly these entry points.
+ *
+ * Conventions
+ *  - every call returns 0 on success, <0 on error (BRISK_E_*); brisk_last_error() gives text.
+ *    The reference has no error channel (absent key -> NULL, brisk/DenseMenuYo.hpp:331-333);
+ *    "absent" is reported through found[] / slot == BRISK_NO_SLOT, never as an error.
+ *  - `bases`/`offsets`: a flat buffer of read characters and n_reads+1 byte offsets, read r =
+ *    bases[offsets[r] .. offsets[r+1]).  Any byte is accepted and coded (c>>1)&3 like
+ *    brisk/Kmers.cpp:442-444 (A=0 C=1 T=2 G=3); reads shorter than k are skipped
+ *    (apps/counter.cpp:233).
+ *  - pointers may be host or device pointers (detected with cudaPointerGetAttributes);
+ *    host buffers are copied inside the call.  No torch types, plain pointers and sizes.
+ *  - a k-mer is given as the reference's kmer_full does (brisk/Kmers.hpp:32-58): the 2k-bit
+ *    value kmer_s (lo, hi words) in the orientation the enumerator chose, plus
+ *    minimizer_idx.  The stored set is keyed on (kmer_s, minimizer_idx) exactly as the
+ *    reference's buckets are (brisk/SuperKmerLight.hpp:209-217).
+ *  - there is no CPU fallback: without a CUDA device brisk_create fails with BRISK_E_CUDA.
+ */
+#ifndef BRISK_B200_H
+#define BRISK_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct brisk_handle brisk_t;
+
+#define BRISK_OK 0
+#define BRISK_E_PARAM (-1)    /* bad k/m/b (Brisk.hpp:50-51 asserts m odd, m < k) or bad argument */
+#define BRISK_E_CUDA (-2)     /* CUDA runtime error, no device, allocation failure */
+#define BRISK_E_CAPACITY (-3) /* an output buffer given by the caller is too small */
+#define BRISK_E_FULL (-4)     /* the bucket store could not grow */
+#define BRISK_E_COMM (-5)     /* NCCL error */
+
+#define BRISK_NO_SLOT (~(uint64_t)0)
+
+/* flags for brisk_create */
+#define BRISK_F_MANAGED 1u        /* store in cudaMallocManaged memory: brisk_data_ptr() is host-dereferenceable */
+#define BRISK_F_LITERAL_DECYCLE 2u /* debug: evaluate DecyclingSet::memDouble literally for every m-mer */
+
+/* one k-mer as the reference's kmer_full carries it */
+typedef struct {
+    uint64_t lo, hi;       /* kmer_s */
+    uint8_t minimizer_idx; /* nucleotide offset of the minimizer from the k-mer's right end */
+    uint8_t pad[7];
+} brisk_kmer;
+
+/* Parameters(k,m,b) + Brisk<DATA>(params): brisk/parameters.hpp:24-34, brisk/Brisk.hpp:47-52.
+ * data_size = sizeof(DATA) (1 for the counter's uint8_t).  capacity_hint = expected number of
+ * distinct stored k-mers (0 = size from the batches seen).  device < 0 = current device. */
+int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size, int device, uint64_t capacity_hint,
+                 uint32_t flags, brisk_t **out);
+int brisk_destroy(brisk_t *h);
+
+/* SuperKmerEnumerator::next over a batch of reads (brisk/Kmers.cpp:509-603): writes one packed
+ * superkmer record per emitted superkmer (rec_words u64 each, layout in DESIGN.md) and returns
+ * their number.  `recs` may be NULL to only count.  Order of records is unspecified. */
+int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                          uint64_t *recs, uint64_t cap_recs, uint64_t *n_recs, uint32_t *rec_words);
+
+/* count_sequence for every read (apps/counter.cpp:231-276): insert_superkmer (brisk/Brisk.hpp:123-147)
+ * fused with the counter's update  new -> 1, else ++ (uint8 wrap, apps/counter.cpp:262-269). */
+int brisk_count_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads);
+
+/* insert_superkmer without touching DATA: slot of every k-mer occurrence in read order (k-mer i of
+ * read r at index sum_{r'<r} max(0,len-k+1) + i) and whether it was newly inserted
+ * (`newly_inserted`, brisk/Brisk.hpp:123).  slots/newly may be NULL. */
+int brisk_insert_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                       uint64_t *slots, uint8_t *newly);
+
+/* query_sequence / get_superkmer (apps/counter.cpp:281-310, brisk/Brisk.hpp:102-118): per k-mer
+ * occurrence in read order, found[i] and the DATA bytes (data_size each; zero when absent). */
+int brisk_get_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                    uint8_t *found, void *data_out);
+
+/* Brisk::insert on explicit k-mers (size-1 superkmers through insert_superkmer).
+ * count != 0 also applies the counter update. */
+int brisk_insert_kmers(brisk_t *h, const brisk_kmer *kmers, uint64_t n, uint64_t *slots, uint8_t *newly,
+                       int count);
+/* Brisk::get (brisk/Brisk.hpp:64-69): slot or BRISK_NO_SLOT, and DATA bytes (nullable outputs). */
+int brisk_get_kmers(brisk_t *h, const brisk_kmer *kmers, uint64_t n, uint64_t *slots, void *data_out);
+
+/* address of the DATA of a slot; host-dereferenceable only with BRISK_F_MANAGED.  Slots are stable
+ * until the store grows (the reference's pointers die at the next bucket realloc, README.md:109-110). */
+void *brisk_data_ptr(brisk_t *h, uint64_t slot);
+
+/* restart_kmer_enumeration + next + get (brisk/Brisk.hpp:166-179): every stored (kmer_s,
+ * minimizer_idx, DATA), unordered.  keys/data may be NULL to only count. */
+int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n);
+
+/* Brisk::stats (brisk/Brisk.hpp:194-197, brisk/DenseMenuYo.hpp:545-568). nb_skmers = superkmer records
+ * that created at least one k-mer; largest_bucket is not tracked (reported 0): both depend on
+ * insertion order in the reference. */
+int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t *nb_kmers,
+                uint64_t *device_bytes, uint64_t *largest_bucket);
+
+/* grow the store so that n_keys distinct k-mers fit (the GPU analogue of Brisk::reallocate) */
+int brisk_reserve(brisk_t *h, uint64_t n_keys);
+int brisk_capacity(brisk_t *h, uint64_t *slots);
+int brisk_sync(brisk_t *h);
+
+/* timing of the last brisk_count_reads / brisk_insert_reads / brisk_get_reads call, measured with CUDA
+ * events on the handle's stream: [0] pack, [1] enumerate, [2] partition, [3] insert/get, [4] whole
+ * device section (ms); n_launches = kernels launched by the call. */
+int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches);
+
+/* ---- multi-GPU: one process per GPU, bucket ids sharded over ranks, superkmers exchanged with NCCL.
+ * id = 128 bytes from brisk_comm_unique_id on rank 0, broadcast by the caller. */
+int brisk_comm_unique_id(uint8_t id[128]);
+int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int n_ranks);
+/* owner rank of a bucket id (pure function; also used by the CPU tests of the routing) */
+uint32_t brisk_owner_of_bucket(uint64_t bucket_id, uint8_t b, uint32_t n_ranks);
+
+const char *brisk_last_error(void);
+const char *brisk_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
