@@ -15,6 +15,7 @@ PROTOTYPES = {
     "brisk_count_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
     "brisk_insert_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_get_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    "brisk_query_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "brisk_insert_kmers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]),
     "brisk_get_kmers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_data_ptr": (C.c_void_p, [C.c_void_p, C.c_uint64]),
@@ -23,6 +24,7 @@ PROTOTYPES = {
     "brisk_reserve": (C.c_int, [C.c_void_p, C.c_uint64]),
     "brisk_capacity": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "brisk_sync": (C.c_int, [C.c_void_p]),
+    "brisk_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]),
     "brisk_comm_unique_id": (C.c_int, [C.c_void_p]),
     "brisk_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),

@@ -122,6 +122,15 @@ class Brisk:
         self._check(self._lib.brisk_get_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), _ptr(found), _ptr(data)))
         return found, (data[:, 0] if self.data_size == 1 else data)
 
+    def query_reads(self, bases, offsets):
+        """(hits, total) — what query_sequence accumulates (apps/counter.cpp:281-310)."""
+        hits, total = C.c_uint64(), C.c_uint64()
+        self._check(self._lib.brisk_query_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), C.byref(hits), C.byref(total)))
+        return hits.value, total.value
+
+    def set_stream(self, cuda_stream):
+        self._check(self._lib.brisk_set_stream(self._h, C.c_void_p(cuda_stream)))
+
     # ---- explicit k-mers
     @staticmethod
     def pack_kmers(lo, hi, idx):

@@ -56,6 +56,7 @@ struct brisk_handle {
     uint32_t data_size = 1;
     uint64_t hint = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[6] = {};
     float last_ms[5] = {0, 0, 0, 0, 0};
     uint32_t last_launches = 0;
@@ -226,7 +227,8 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     h->flags = flags;
     h->data_size = data_size;
     h->hint = capacity_hint;
-    CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
@@ -262,7 +264,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaFree(h->overflow);
     cudaFree(h->d_rec_count);
     for (int i = 0; i < 6; i++) cudaEventDestroy(h->ev[i]);
-    cudaStreamDestroy(h->stream);
+    cudaStreamDestroy(h->own_stream);
     delete h;
     return BRISK_OK;
 }
@@ -451,7 +453,7 @@ static void finish_timing(brisk_handle *h) {
 
 // shared driver of count / insert / get over reads
 static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, int mode,
-                     uint64_t *slots, uint8_t *flags, void *data_out) {
+                     uint64_t *slots, uint8_t *flags, void *data_out, uint64_t *agg_out = nullptr) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     if (n_reads && (!bases || !offsets)) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::mutex> lock(h->mu);
@@ -472,7 +474,11 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     }
     OccOut O;
     O.rec_occ = with_occ ? (const u64 *)h->d_rec_occ.p : nullptr;
-    O.slots = nullptr; O.flags = nullptr; O.data = nullptr;
+    O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
+    if (agg_out) {
+        CK(cudaMemsetAsync(h->counters + 5, 0, 2 * sizeof(uint64_t), h->stream));
+        O.agg = h->counters + 5;
+    }
     // per-occurrence outputs go through device staging when the caller's buffers are on the host
     bool s_dev = is_device_ptr(slots), f_dev = is_device_ptr(flags), d_dev = is_device_ptr(data_out);
     if (slots) {
@@ -493,6 +499,7 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     if (slots && !s_dev) CK(cudaMemcpyAsync(slots, O.slots, n_occ * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     if (flags && !f_dev) CK(cudaMemcpyAsync(flags, O.flags, n_occ, cudaMemcpyDeviceToHost, h->stream));
     if (data_out && !d_dev) CK(cudaMemcpyAsync(data_out, O.data, n_occ * h->data_size, cudaMemcpyDeviceToHost, h->stream));
+    if (agg_out) CK(cudaMemcpyAsync(agg_out, h->counters + 5, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     if (mode != MODE_GET) {
         rc = settle(h);
         if (rc) return rc;
@@ -501,6 +508,15 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     }
     finish_timing(h);
     return BRISK_OK;
+}
+
+extern "C" int brisk_query_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *hits,
+                                 uint64_t *total) {
+    uint64_t agg[2] = {0, 0};
+    int rc = run_reads(h, bases, offsets, n_reads, MODE_GET, nullptr, nullptr, nullptr, agg);
+    if (hits) *hits = agg[0];
+    if (total) *total = agg[1];
+    return rc;
 }
 
 extern "C" int brisk_count_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads) {
@@ -679,6 +695,14 @@ extern "C" int brisk_sync(brisk_t *h) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
+    return BRISK_OK;
+}
+extern "C" int brisk_set_stream(brisk_t *h, void *stream) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    std::lock_guard<std::mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    h->stream = stream ? (cudaStream_t)stream : h->own_stream;
     return BRISK_OK;
 }
 extern "C" int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches) {

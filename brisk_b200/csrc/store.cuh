@@ -190,6 +190,7 @@ struct OccOut {
     u64 *slots;          // per occurrence (nullable)
     unsigned char *flags;  // per occurrence: newly (insert) / found (get) (nullable)
     unsigned char *data;   // per occurrence data_size bytes (get, nullable)
+    u64 *agg;              // get: [0] += hits, [1] += sum of the DATA bytes of the hits (nullable)
 };
 
 // One warp takes 32 records at a time and spreads their k-mers over its lanes, so that every lane runs
@@ -202,6 +203,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
     const u64 n_warps = ((u64)gridDim.x * blockDim.x) >> 5;
     const u64 top_mask = rec_payload_mask_top(P);
     u32 new_keys = 0, new_recs = 0;
+    u64 agg_hits = 0, agg_sum = 0;
     for (u64 r0 = warp * 32; r0 < n_recs; r0 += n_warps * 32) {
         const u64 ri = r0 + lane;
         u64 w[RW];
@@ -256,6 +258,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                 if (MODE == MODE_GET) {
                     u32 mt = 0;
                     bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
+                    if (found) { agg_hits++; agg_sum += mt >> 24; }
                     if (O.rec_occ) {
                         u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
                         if (O.flags) O.flags[oi] = found;
@@ -284,6 +287,14 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                 }
             }
         }
+    }
+    if (MODE == MODE_GET && O.agg) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            agg_hits += __shfl_xor_sync(0xffffffffu, agg_hits, d);
+            agg_sum += __shfl_xor_sync(0xffffffffu, agg_sum, d);
+        }
+        if (lane == 0 && agg_hits) { atomicAdd(O.agg, agg_hits); atomicAdd(O.agg + 1, agg_sum); }
     }
     if (MODE != MODE_GET) {
 #pragma unroll

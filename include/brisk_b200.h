@@ -81,6 +81,11 @@ int brisk_insert_reads(brisk_t *h, const char *bases, const uint64_t *offsets, u
 int brisk_get_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
                     uint8_t *found, void *data_out);
 
+/* query_sequence as the counter app uses it (apps/counter.cpp:281-310): number of k-mer occurrences found and
+ * the sum of their DATA bytes (`total`), nothing per occurrence. */
+int brisk_query_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *hits,
+                      uint64_t *total);
+
 /* Brisk::insert on explicit k-mers (size-1 superkmers through insert_superkmer).
  * count != 0 also applies the counter update. */
 int brisk_insert_kmers(brisk_t *h, const brisk_kmer *kmers, uint64_t n, uint64_t *slots, uint8_t *newly,
@@ -106,6 +111,8 @@ int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t 
 int brisk_reserve(brisk_t *h, uint64_t n_keys);
 int brisk_capacity(brisk_t *h, uint64_t *slots);
 int brisk_sync(brisk_t *h);
+/* run every later call on the caller's CUDA stream (cudaStream_t; NULL = the handle's own stream) */
+int brisk_set_stream(brisk_t *h, void *stream);
 
 /* timing of the last brisk_count_reads / brisk_insert_reads / brisk_get_reads call, measured with CUDA
  * events on the handle's stream: [0] pack, [1] enumerate, [2] partition, [3] insert/get, [4] whole

@@ -16,6 +16,8 @@
 //   ref_dump count reads.txt k m b out.bin     count like apps/counter.cpp, dump the index
 //   ref_dump query reads.txt k m b out.bin q.txt   count reads.txt, then query q.txt
 //   ref_dump time  reads.txt k m b threads [max_reads]   timed count (hot path only)
+//   ref_dump steps reads.txt k m b threads reads_per_step n_steps
+//                  step j = count chunk j (count_sequence) then query chunk j-1 (query_sequence), timed
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -216,6 +218,50 @@ int main(int argc, char **argv) {
         double cnt = chrono::duration<double>(t2 - t1).count();
         printf("threads %d\nreads %lu\noccurrences %lu\nctor_s %.6f\ncount_s %.6f\n", threads, reads.size(),
                occ, ctor, cnt);
+        print_stats(index);
+        return 0;
+    }
+    if (mode == "steps") {
+        int threads = atoi(argv[6]);
+        size_t per = strtoull(argv[7], 0, 10);
+        size_t n_steps = strtoull(argv[8], 0, 10);
+        vector<string> reads = load_reads(argv[2], per * n_steps);
+        auto t0 = chrono::steady_clock::now();
+        Brisk<uint8_t> index(params);
+        double ctor = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
+        printf("threads %d\nctor_s %.6f\n", threads, ctor);
+        for (size_t j = 0; j < n_steps; j++) {
+            size_t lo = j * per, hi = min(reads.size(), (j + 1) * per);
+            uint64_t occ = 0, qocc = 0, hits = 0, total = 0;
+            for (size_t r = lo; r < hi; r++) occ += reads[r].size() >= k ? reads[r].size() - k + 1 : 0;
+            auto a = chrono::steady_clock::now();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 64)
+            for (size_t r = lo; r < hi; r++) count_read(index, reads[r]);
+            auto b2 = chrono::steady_clock::now();
+            if (j > 0) {
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 64) reduction(+ : qocc, hits, total)
+                for (size_t r = lo - per; r < lo; r++) {
+                    string &s = reads[r];
+                    if (s.size() < k) continue;
+                    SuperKmerEnumerator en(s, k, m, params.dede);
+                    vector<kmer_full> sk;
+                    en.next(sk);
+                    while (sk.size() > 0) {
+                        vector<uint8_t *> v = index.get_superkmer(sk);
+                        for (uint8_t *p : v) {
+                            qocc++;
+                            if (p) { total += *p; hits++; }
+                        }
+                        sk.clear();
+                        en.next(sk);
+                    }
+                }
+            }
+            auto c = chrono::steady_clock::now();
+            printf("step %lu %.6f %.6f %lu %lu %lu %lu\n", j, chrono::duration<double>(b2 - a).count(),
+                   chrono::duration<double>(c - b2).count(), occ, qocc, hits, total);
+            fflush(stdout);
+        }
         print_stats(index);
         return 0;
     }
