@@ -221,6 +221,9 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     if (device < 0) CK(cudaGetDevice(&device));
     if (device >= ndev) return fail(BRISK_E_PARAM, "device index out of range");
     CK(cudaSetDevice(device));
+    // the store is probed at random: fetch single 32-byte sectors from HBM instead of 64-byte pairs
+    cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 32);
+    cudaGetLastError();
     brisk_handle *h = new brisk_handle();
     h->P = P;
     h->device = device;

@@ -112,6 +112,18 @@ struct EnumOut {
     const u64 *kmer_base;  // optional [n_reads]: occurrence index of k-mer 0 of each read
 };
 
+// 64-bit minimum over the warp
+__device__ __forceinline__ u64 warp_min64(u64 v) {
+    u32 hi = (u32)(v >> 32), lo = (u32)v;
+    u32 mhi = __reduce_min_sync(0xffffffffu, hi);
+    u32 mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    return ((u64)mhi << 32) | mlo;
+}
+
+// ring of order hashes: slot-major, the column is XOR-swizzled with the slot so that a thread writing its own
+// column and a warp reading one thread's column across slots are both free of bank conflicts
+__device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_THREADS + (tid ^ (slot & 31)); }
+
 template <int RW>
 __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 n_reads,
@@ -127,6 +139,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     __shared__ u64 rd_id[ENUM_THREADS];
 
     const int tid = threadIdx.x;
+    const int lane = tid & 31;
     const int k = P.k, m = P.m;
     const u64 rid = (u64)blockIdx.x * ENUM_THREADS + tid;
     u32 L = 0;
@@ -150,60 +163,13 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     // rolling state
     u64 f = 0, r = 0, word = 0, revbits = 0;
     double Ar = 0, Ai = 0, Br = 0, Bi = 0;
-    int rslot = -1;           // ring slot of the newest m-mer
+    int rslot = -1;           // ring slot of the newest m-mer (the same for every thread: all reads start at t = 0)
     u64 H = 0;                // mini_hash
     int pos = 0;              // mini_pos
     bool rev = false;         // reversed
     u32 i0 = 0;               // first k-mer of the open superkmer
     int pos0 = 0;             // mini_pos of that k-mer
     const int rshift = 2 * m - 2;
-
-    // get_minimizer(kk-mer ending at base t) -> (H, pos, rev), Kmers.cpp:367-408 literally
-    auto rescan = [&](int kk, u32 t) {
-        const int nmax = kk - m;
-        const int real_max = kk > 32 ? 32 - m : nmax;
-        u64 cur64 = 0;
-        if (kk > 32) cur64 = get_bits64(pk, (u64)t - 31);
-        u64 hm = ring[rslot * ENUM_THREADS + tid];
-        bool rv0 = revbits & 1;
-        int mp = 0;
-        int canon_state = -1;  // lazily evaluated canonized(seq, kk)
-        for (int i = 1; i <= nmax; i++) {
-            u64 nh;
-            bool rv;
-            if (i <= real_max) {
-                int sl = rslot - i;
-                if (sl < 0) sl += P.w;
-                nh = ring[sl * ENUM_THREADS + tid];
-                rv = (revbits >> i) & 1;
-            } else if (i >= 32) {
-                nh = P.polyA_hash;
-                rv = false;
-            } else {
-                u64 v = cur64 >> (2 * i);
-                u64 rc = rcbc(v, m);
-                u64 c = v < rc ? v : rc;
-                nh = bfc_hash_literal(coef, P.eps, c, P.m_mask, m);
-                rv = c != v;
-            }
-            if (nh < hm) {
-                mp = i; rv0 = rv; hm = nh;
-            } else if (nh == hm) {
-                if (nmax - i < mp) {
-                    mp = nmax - i; rv0 = rv;
-                } else if (nmax - i == mp) {
-                    if (canon_state < 0) {
-                        int nlo = kk < 32 ? kk : 32;
-                        u64 lo = get_bases(pk, (u64)t + 1 - nlo, nlo);
-                        u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
-                        canon_state = canonized128(lo, hi, kk) ? 1 : 0;
-                    }
-                    if (!canon_state) { mp = nmax - i; rv0 = false; }
-                }
-            }
-        }
-        H = hm; pos = mp; rev = rv0;
-    };
 
     auto append = [&](u32 a, int n, int p0, bool rv) {
         u32 slot = atomicAdd(&pool_n, 1u);
@@ -222,7 +188,13 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
 
     for (u32 t0 = 0; t0 < maxL; t0 += ENUM_SYNC_STEPS) {
         for (u32 t = t0; t < t0 + ENUM_SYNC_STEPS; t++) {
-            if (t < L) {
+            const bool active = t < L;
+            u64 h = 0;
+            bool rv = false;
+            int need_kk = 0;  // k-1: seed get_minimizer (Kmers.cpp:533), k: the minimizer left the window (:551-562)
+            const bool old_rev = rev;
+            if (t + 1 >= (u32)m) rslot = rslot + 1 == P.w ? 0 : rslot + 1;  // same t in every thread: uniform
+            if (active) {
                 if ((t & 31) == 0) word = __ldg(pk + (t >> 5));
                 const u32 code = (u32)(word >> 62);
                 word <<= 2;
@@ -251,7 +223,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                     }
                 }
                 if (t + 1 >= (u32)m) {
-                    const bool rv = r < f;
+                    rv = r < f;
                     const u64 canon = rv ? r : f;
                     u32 cls;
                     if (P.literal_decycle) {
@@ -268,34 +240,92 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                         if (fabs(fabs(R) - P.eps) < P.guard || fabs(fabs(R2) - P.eps) < P.guard)
                             cls = dec_mem_double(coef, P.eps, canon, m);
                     }
-                    const u64 h = ((u64)cls << 62) + bfc_mix(canon, P.m_mask);
-                    rslot = rslot + 1 == P.w ? 0 : rslot + 1;
-                    ring[rslot * ENUM_THREADS + tid] = h;
+                    h = ((u64)cls << 62) + bfc_mix(canon, P.m_mask);
+                    ring[ring_at(rslot, tid)] = h;
                     revbits = (revbits << 1) | (u64)rv;
-
                     if (t + 2 == (u32)k) {
-                        rescan(k - 1, t);  // Kmers.cpp:533-534
+                        need_kk = k - 1;
                     } else if (t + 1 >= (u32)k) {
-                        const u32 i = t + 1 - k;
-                        const bool old_rev = rev;
-                        bool boundary = false;
                         pos += 1;
-                        if (pos > k - m) {
-                            boundary = true;
-                            rescan(k, t);
-                        } else if (h < H) {
-                            boundary = true;
-                            H = h; pos = 0; rev = rv;
-                        }
-                        if (i == 0) {
-                            pos0 = pos;
-                        } else if (boundary) {
-                            append(i0, (int)(i - i0), pos0, old_rev);
-                            i0 = i; pos0 = pos;
-                        }
-                        if (t + 1 == L) append(i0, (int)(i + 1 - i0), pos0, rev);
+                        if (pos > k - m) need_kk = k;
                     }
                 }
+            }
+            __syncwarp();
+            // get_minimizer (Kmers.cpp:367-408) for the threads that asked, one requester at a time, the warp's
+            // lanes taking one window position each
+            unsigned req = __ballot_sync(0xffffffffu, need_kk != 0);
+            if (req) {
+                const int kk = (t + 2 == (u32)k) ? k - 1 : k;
+                const int nmax = kk - m;
+                const int real_max = kk > 32 ? 32 - m : nmax;
+                const bool has_hi = nmax >= 32;  // positions >= 32 hold the all-A pseudo m-mer (Q3)
+                u64 cur64 = 0;
+                if (need_kk && kk > 32) cur64 = get_bits64(pk, (u64)t - 31);
+                while (req) {
+                    const int src = __ffs(req) - 1;
+                    req &= req - 1;
+                    const u64 s_cur = __shfl_sync(0xffffffffu, cur64, src);
+                    const u64 s_revbits = __shfl_sync(0xffffffffu, revbits, src);
+                    const int s_tid = (tid & ~31) | src;
+                    u64 nh = ~0ull;
+                    bool prv = false;
+                    if (lane <= nmax) {
+                        if (lane <= real_max) {
+                            int sl = rslot - lane;
+                            if (sl < 0) sl += P.w;
+                            nh = ring[ring_at(sl, s_tid)];
+                            prv = (s_revbits >> lane) & 1;
+                        } else {
+                            u64 v = s_cur >> (2 * lane);
+                            u64 rc = rcbc(v, m);
+                            u64 c = v < rc ? v : rc;
+                            nh = bfc_hash_literal(coef, P.eps, c, P.m_mask, m);
+                            prv = c != v;
+                        }
+                    }
+                    u64 hm = warp_min64(nh);
+                    if (has_hi && P.polyA_hash < hm) hm = P.polyA_hash;
+                    u64 tmask = __ballot_sync(0xffffffffu, nh == hm);
+                    if (has_hi && P.polyA_hash == hm) tmask |= ((((u64)1) << (nmax - 31)) - 1) << 32;
+                    const unsigned rvlo = __ballot_sync(0xffffffffu, prv);
+                    int mp = __ffsll((long long)tmask) - 1;
+                    bool rv0 = mp < 32 ? (rvlo >> mp) & 1u : false;
+                    u64 rest = tmask & (tmask - 1);
+                    if (rest) {  // equal hashes in the window: the tie rules of Kmers.cpp:389-404, in scan order
+                        int cs = 0;
+                        if (lane == src) {
+                            int nlo = kk < 32 ? kk : 32;
+                            u64 lo = get_bases(pk, (u64)t + 1 - nlo, nlo);
+                            u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
+                            cs = canonized128(lo, hi, kk) ? 1 : 0;
+                        }
+                        cs = __shfl_sync(0xffffffffu, cs, src);
+                        while (rest) {
+                            const int i2 = __ffsll((long long)rest) - 1;
+                            rest &= rest - 1;
+                            const bool rvi = i2 < 32 ? (rvlo >> i2) & 1u : false;
+                            if (nmax - i2 < mp) { mp = nmax - i2; rv0 = rvi; }
+                            else if (nmax - i2 == mp) { if (!cs) rv0 = false; }
+                        }
+                    }
+                    if (lane == src) { H = hm; pos = mp; rev = rv0; }
+                }
+            }
+            if (active && t + 1 >= (u32)k) {
+                const u32 i = t + 1 - k;
+                bool boundary = need_kk != 0;
+                if (!boundary && h < H) {
+                    boundary = true;
+                    H = h; pos = 0; rev = rv;
+                }
+                if (i == 0) {
+                    pos0 = pos;
+                } else if (boundary) {
+                    append(i0, (int)(i - i0), pos0, old_rev);
+                    i0 = i; pos0 = pos;
+                }
+                if (t + 1 == L) append(i0, (int)(i + 1 - i0), pos0, rev);
             }
         }
         __syncthreads();
@@ -313,11 +343,11 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                     if (g >= out.rec_cap) break;
                     u64 d = pool[e];
                     int owner = (int)(d >> 49) & 127;
-                    bool rv = (d >> 48) & 1;
+                    bool rvd = (d >> 48) & 1;
                     u64 rec[RW];
-                    build_record<RW>(P, packed + rd_start[owner], (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rv, rec);
+                    build_record<RW>(P, packed + rd_start[owner], (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd, rec);
                     store_record<RW>(out.recs, g, rec);
-                    if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rd_id[owner]] + (u32)d) << 1) | (u64)rv;
+                    if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rd_id[owner]] + (u32)d) << 1) | (u64)rvd;
                 }
             }
             __syncthreads();
