@@ -144,17 +144,37 @@ __device__ __forceinline__ u64 get_bits64(const u64 *pk, u64 a) {
 __device__ __forceinline__ u64 get_bases(const u64 *pk, u64 a, int len) { return len ? get_bits64(pk, a) >> (64 - 2 * len) : 0; }
 
 // ---------------------------------------------------------------- multiword helpers (registers)
-// 64 bits of the little-endian multiword value v[NW] starting at bit sh
-template <int NW>
-__device__ __forceinline__ u64 mw_extract64(const u64 (&v)[NW], int sh) {
-    int q = sh >> 6, r = sh & 63;
-    u64 lo = 0, hi = 0;
+// Shifts the little-endian multiword value v[NW] right by sh bits, in place.  Whole-word moves are done as
+// log-steps with static indices so that v[] stays in registers (a dynamically indexed v[q] would be spilled
+// to local memory, which the first ncu capture showed as one extra DRAM sector write per k-mer).
+template <int NW, int MAXQ>
+__device__ __forceinline__ void mw_shr(u64 (&v)[NW], int sh) {
+    const int q = sh >> 6, r = sh & 63;
+    if (MAXQ >= 1 && (q & 1)) {
 #pragma unroll
-    for (int i = 0; i < NW; i++) {
-        if (i == q) lo = v[i];
-        if (i == q + 1) hi = v[i];
+        for (int i = 0; i < NW; i++) v[i] = i + 1 < NW ? v[i + 1] : 0ull;
     }
-    return r ? (lo >> r) | (hi << (64 - r)) : lo;
+    if (MAXQ >= 2 && (q & 2)) {
+#pragma unroll
+        for (int i = 0; i < NW; i++) v[i] = i + 2 < NW ? v[i + 2] : 0ull;
+    }
+    if (MAXQ >= 4 && (q & 4)) {
+#pragma unroll
+        for (int i = 0; i < NW; i++) v[i] = i + 4 < NW ? v[i + 4] : 0ull;
+    }
+    if (r) {
+#pragma unroll
+        for (int i = 0; i < NW; i++) v[i] = (v[i] >> r) | (i + 1 < NW ? v[i + 1] << (64 - r) : 0ull);
+    }
+}
+// 64 bits of v[NW] starting at bit sh (v is not modified)
+template <int NW, int MAXQ>
+__device__ __forceinline__ u64 mw_extract64(const u64 (&v)[NW], int sh) {
+    u64 t[NW];
+#pragma unroll
+    for (int i = 0; i < NW; i++) t[i] = v[i];
+    mw_shr<NW, MAXQ>(t, sh);
+    return t[0];
 }
 
 // ---------------------------------------------------------------- record layout

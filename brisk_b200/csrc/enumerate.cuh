@@ -77,22 +77,13 @@ __device__ __forceinline__ void build_record(const BriskParams &P, const u64 *pk
         u64 t[RW];
 #pragma unroll
         for (int wi = 0; wi < RW; wi++) t[wi] = rev2(rec[RW - 1 - wi] ^ 0xaaaaaaaaaaaaaaaaull);
-        int sh = 64 * RW - 2 * len;
-        int q = sh >> 6, r = sh & 63;
 #pragma unroll
-        for (int wi = 0; wi < RW; wi++) {
-            u64 lo = 0, hi = 0;
-#pragma unroll
-            for (int j = 0; j < RW; j++) {
-                if (j == wi + q) lo = t[j];
-                if (j == wi + q + 1) hi = t[j];
-            }
-            rec[wi] = r ? (lo >> r) | (hi << (64 - r)) : lo;
-        }
+        for (int wi = 0; wi < RW; wi++) rec[wi] = t[wi];
+        mw_shr<RW, 7>(rec, 64 * RW - 2 * len);
         idx0 = P.k - P.m - pos0 - n + 1;
     }
     // minimizer slice of the first emitted k-mer: nucleotides [idx0, idx0+m) from its right end
-    u64 W = mw_extract64<RW>(rec, 2 * (n - 1 + idx0)) & P.m_mask;
+    u64 W = mw_extract64<RW, 3>(rec, 2 * (n - 1 + idx0)) & P.m_mask;
     u64 bucket = (bfc_mix(W, P.m_mask) >> (2 * P.s)) & P.bucket_mask;
     rec[RW - 1] |= rec_header(P, bucket, n, idx0);
 }

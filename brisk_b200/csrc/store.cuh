@@ -173,14 +173,12 @@ __device__ __forceinline__ void store_park(const StoreView &T, u64 lo, u64 hi, u
 // k-mer j (emission order) of a record whose payload words are pw[] (header already masked off)
 template <int RW, int KW>
 __device__ __forceinline__ void record_kmer(const BriskParams &P, const u64 (&pw)[RW], int n, int j, u64 &lo, u64 &hi) {
-    int sh = 2 * (n - 1 - j);
-    lo = mw_extract64<RW>(pw, sh);
-    if (KW == 2) {
-        hi = mw_extract64<RW>(pw, sh + 64) & P.kmask_hi;
-    } else {
-        hi = 0;
-    }
-    lo &= P.kmask_lo;
+    u64 t[RW];
+#pragma unroll
+    for (int i = 0; i < RW; i++) t[i] = pw[i];
+    mw_shr<RW, 1>(t, 2 * (n - 1 - j));  // n <= w <= 64: at most 126 bits
+    lo = t[0] & P.kmask_lo;
+    hi = KW == 2 ? (t[1] & P.kmask_hi) : 0ull;
 }
 
 enum { MODE_COUNT = 0, MODE_INSERT = 1, MODE_GET = 2 };
