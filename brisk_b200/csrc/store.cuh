@@ -20,7 +20,6 @@
 #define STORE_MAX_PROBE 8192u
 #define META_TAG_MASK 0xFFu
 #define META_COUNT_ONE (1u << 24)
-#define REC_U 4
 
 struct Slot1 { u64 key; u32 meta; u32 aux; };
 struct Slot2 { u64 lo, hi; u32 meta; u32 aux; u64 aux2; };
@@ -64,7 +63,7 @@ __device__ __forceinline__ u32 *slot_meta_ptr(const StoreView &T, u64 slot) {
 // find-or-claim (kmer_s, idx).  add = increment applied to meta (META_COUNT_ONE for the counter, 0 for a
 // plain insert).  Returns 0 = found, 1 = newly inserted, -1 = probe limit reached (nothing changed).
 template <int KW>
-__device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 home, u64 &slot_out) {
+__device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 &slot_out) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
@@ -75,7 +74,7 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
         return res;
     }
     S *tab = reinterpret_cast<S *>(T.slots);
-    u64 s = home;
+    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
     u32 probes = 0;
     while (probes < STORE_MAX_PROBE) {
         S *p = tab + s;
@@ -124,7 +123,7 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
 
 // lookup only; returns true and the slot when present
 template <int KW>
-__device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 home, u64 &slot_out, u32 &meta_out) {
+__device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 &slot_out, u32 &meta_out) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
@@ -134,7 +133,7 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
         return (mt & META_TAG_MASK) == tag;
     }
     const S *tab = reinterpret_cast<const S *>(T.slots);
-    u64 s = home;
+    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
     for (u32 probes = 0; probes < STORE_MAX_PROBE;) {
         const S *p = tab + s;
         bool match;
@@ -230,53 +229,36 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
             if (lane >= d) incl += v;
         }
         const int total = __shfl_sync(0xffffffffu, incl, 31);
-        // U occurrences per lane and round: phase 1 forms the keys and prefetches their home slots, phase 2 runs
-        // the table operations, so that U independent HBM accesses per lane are in flight instead of one
-        for (int c = 0; c < total; c += 32 * REC_U) {
-            u64 k_lo[REC_U], k_hi[REC_U], k_oi[REC_U], k_home[REC_U];
-            u32 k_meta[REC_U];  // idx | first-of-record << 8 | valid << 9
-            u64 k_bucket[REC_U];
+        for (int c = 0; c < total; c += 32) {
+            const int o = c + lane;
+            // source lane = number of lanes whose inclusive prefix is <= o
+            int src = 0;
 #pragma unroll
-            for (int u = 0; u < REC_U; u++) {
-                const int o = c + 32 * u + lane;
-                int src = 0;
-#pragma unroll
-                for (int step = 16; step > 0; step >>= 1) {
-                    int probe = __shfl_sync(0xffffffffu, incl, (src + step - 1) & 31);
-                    if (probe <= o) src += step;
-                }
-                const int src_l = src & 31;
-                const int s_incl = __shfl_sync(0xffffffffu, incl, src_l);
-                const int s_n = __shfl_sync(0xffffffffu, n, src_l);
-                const int s_idx0 = __shfl_sync(0xffffffffu, idx0, src_l);
-                k_bucket[u] = __shfl_sync(0xffffffffu, bucket, src_l);
-                const u64 s_occ = __shfl_sync(0xffffffffu, occ, src_l);
-                u64 pw[RW];
-#pragma unroll
-                for (int i = 0; i < RW; i++) pw[i] = __shfl_sync(0xffffffffu, w[i], src_l);
-                const bool valid = o < total;
-                const int j = valid ? o - (s_incl - s_n) : 0;
-                record_kmer<RW, KW>(P, pw, valid ? s_n : 1, j, k_lo[u], k_hi[u]);
-                const u32 idx = (u32)(s_idx0 + j);
-                k_meta[u] = idx | ((j == 0) << 8) | ((u32)valid << 9);
-                k_oi[u] = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
-                k_home[u] = slot_hash(k_lo[u], KW == 1 ? 0 : k_hi[u], idx) & T.mask;
-                if (valid) {
-                    const char *p = reinterpret_cast<const char *>(T.slots) + k_home[u] * sizeof(typename SlotOf<KW>::type);
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-                }
+            for (int step = 16; step > 0; step >>= 1) {
+                int probe = __shfl_sync(0xffffffffu, incl, (src + step - 1) & 31);
+                if (src + step <= 32 && probe <= o) src += step;
             }
+            const int src_l = src & 31;
+            const int s_incl = __shfl_sync(0xffffffffu, incl, src_l);
+            const int s_n = __shfl_sync(0xffffffffu, n, src_l);
+            const int s_idx0 = __shfl_sync(0xffffffffu, idx0, src_l);
+            const u64 s_bucket = __shfl_sync(0xffffffffu, bucket, src_l);
+            const u64 s_occ = __shfl_sync(0xffffffffu, occ, src_l);
+            u64 pw[RW];
 #pragma unroll
-            for (int u = 0; u < REC_U; u++) {
-                if (!(k_meta[u] & 512u)) continue;
-                const u64 lo = k_lo[u], hi = k_hi[u], oi = k_oi[u];
-                const u32 idx = k_meta[u] & 255u;
+            for (int i = 0; i < RW; i++) pw[i] = __shfl_sync(0xffffffffu, w[i], src_l);
+            if (o < total) {
+                const int j = o - (s_incl - s_n);
+                u64 lo, hi;
+                record_kmer<RW, KW>(P, pw, s_n, j, lo, hi);
+                const u32 idx = (u32)(s_idx0 + j);
                 u64 slot = ~0ull;
                 if (MODE == MODE_GET) {
                     u32 mt = 0;
-                    bool found = store_find<KW>(T, lo, hi, idx, k_home[u], slot, mt);
+                    bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
                     if (found) { agg_hits++; agg_sum += mt >> 24; }
                     if (O.rec_occ) {
+                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
                         if (O.flags) O.flags[oi] = found;
                         if (O.slots) O.slots[oi] = found ? slot : ~0ull;
                         if (O.data) {
@@ -287,15 +269,16 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                     }
                 } else {
                     const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
-                    int res = store_upsert<KW>(T, lo, hi, idx, add, k_home[u], slot);
+                    int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
                     if (res == 1) {
                         new_keys++;
-                        if (k_meta[u] & 256u) new_recs++;
-                        store_note_new(T, k_bucket[u]);
+                        if (j == 0) new_recs++;
+                        store_note_new(T, s_bucket);
                     } else if (res < 0) {
                         store_park(T, lo, hi, idx, add);
                     }
                     if (O.rec_occ) {
+                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
                         if (O.flags) O.flags[oi] = res == 1;
                         if (O.slots) O.slots[oi] = res < 0 ? ~0ull : slot;
                     }
@@ -338,7 +321,7 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
             u64 slot = ~0ull;
             if (MODE == MODE_GET) {
                 u32 mt = 0;
-                bool found = store_find<KW>(T, lo, hi, idx, slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask, slot, mt);
+                bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
                 if (slots) slots[i] = found ? slot : ~0ull;
                 if (flags) flags[i] = found;
                 if (data) {
@@ -347,7 +330,7 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
                 }
             } else {
                 const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
-                int res = store_upsert<KW>(T, lo, hi, idx, add, slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask, slot);
+                int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
                 if (res == 1) {
                     new_keys++;
                     store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
@@ -372,7 +355,7 @@ __global__ void __launch_bounds__(256) replay_kernel(const BriskParams P, const 
         u64 lo = parked[3 * i], hi = parked[3 * i + 1], x = parked[3 * i + 2];
         u32 idx = (u32)(x & 0xFF), add = (u32)(x >> 8);
         u64 slot;
-        int res = store_upsert<KW>(T, lo, hi, idx, add, slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask, slot);
+        int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
         if (res == 1) {
             atomicAdd(T.counters + 0, 1ull);
             store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
