@@ -184,8 +184,8 @@ static int grow_to(brisk_handle *h, uint64_t new_cap) {
         StoreView to = from;
         to.slots = ns; to.mask = new_cap - 1; to.data = nd;
         int blocks = (int)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
-        if (h->P.key_words == 1) rehash_kernel<1><<<blocks, 256, 0, h->stream>>>(from, to);
-        else rehash_kernel<2><<<blocks, 256, 0, h->stream>>>(from, to);
+        if (h->P.key_words == 1) rehash_kernel<1><<<blocks, 256, 0, h->stream>>>(h->P, from, to);
+        else rehash_kernel<2><<<blocks, 256, 0, h->stream>>>(h->P, from, to);
         CK(cudaGetLastError());
         if (h->data) {  // DATA of the special key follows the arena's end
             CK(cudaMemcpyAsync(nd + new_cap * h->data_size, h->data + h->cap * h->data_size, 64 * (size_t)h->data_size,

@@ -208,6 +208,35 @@ __host__ __device__ __forceinline__ u64 slot_hash(u64 lo, u64 hi, u32 idx) {
     return x;
 }
 
+// ---- placement in the bucket store -----------------------------------------------------------------
+// All k-mers of a superkmer share the m-mer found at minimizer_idx (the minimizer, as it is written in the
+// superkmer's orientation) and have consecutive minimizer_idx.  The home slot of (kmer_s, idx) is therefore
+//     group_base(minimizer m-mer) + idx
+// so that the n k-mers of a superkmer sit in n CONSECUTIVE slots: the lanes of a warp that walk a superkmer
+// touch whole 128-byte lines instead of n random 32-byte sectors.  Collisions jump by STORE_STRIDE (>= the
+// largest superkmer), which keeps a displaced piece of a superkmer contiguous; after STORE_GROUP_PROBES jumps
+// the probe sequence switches to a per-key hash so that a minimizer shared by very many k-mers (low-complexity
+// sequence) cannot build a long chain.
+#define STORE_STRIDE 64u
+#define STORE_GROUP_PROBES 4u
+__host__ __device__ __forceinline__ u64 minimizer_word(const BriskParams &P, u64 lo, u64 hi, int idx) {
+    int sh = 2 * idx;
+    u64 W = sh == 0 ? lo : (sh >= 64 ? hi >> (sh - 64) : (lo >> sh) | (hi << (64 - sh)));
+    return W & P.m_mask;
+}
+__host__ __device__ __forceinline__ u64 group_base(u64 W) {
+    u64 x = (W + 0x9E3779B97F4A7C15ull) * 0xD6E8FEB86659FD93ull;
+    x ^= x >> 32;
+    x *= 0xD6E8FEB86659FD93ull;
+    x ^= x >> 29;
+    return x;
+}
+// slot visited by probe number i (i = 0 is the home slot)
+__host__ __device__ __forceinline__ u64 probe_slot(u64 home, u64 lo, u64 hi, u32 idx, u32 i, u64 mask) {
+    if (i < STORE_GROUP_PROBES) return (home + (u64)i * STORE_STRIDE) & mask;
+    return (slot_hash(lo, hi, idx) + (i - STORE_GROUP_PROBES)) & mask;
+}
+
 // bucket id of a k-mer (brisk/Brisk.hpp:135-137 after hash_kmer_minimizer_inplace, Kmers.cpp:191-200):
 // middle 2b bits of the hashed m-mer found at minimizer_idx
 __host__ __device__ __forceinline__ u64 bucket_of_kmer(const BriskParams &P, u64 lo, u64 hi, int idx) {

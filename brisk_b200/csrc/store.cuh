@@ -63,7 +63,7 @@ __device__ __forceinline__ u32 *slot_meta_ptr(const StoreView &T, u64 slot) {
 // find-or-claim (kmer_s, idx).  add = increment applied to meta (META_COUNT_ONE for the counter, 0 for a
 // plain insert).  Returns 0 = found, 1 = newly inserted, -1 = probe limit reached (nothing changed).
 template <int KW>
-__device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 &slot_out) {
+__device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 home, u64 &slot_out) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
@@ -74,7 +74,7 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
         return res;
     }
     S *tab = reinterpret_cast<S *>(T.slots);
-    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
+    u64 s = home;
     u32 probes = 0;
     while (probes < STORE_MAX_PROBE) {
         S *p = tab + s;
@@ -115,15 +115,15 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
                 return 0;
             }
         }
-        s = (s + 1) & T.mask;
         probes++;
+        s = probe_slot(home, lo, KW == 1 ? 0 : hi, idx, probes, T.mask);
     }
     return -1;
 }
 
 // lookup only; returns true and the slot when present
 template <int KW>
-__device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 &slot_out, u32 &meta_out) {
+__device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 home, u64 &slot_out, u32 &meta_out) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
@@ -133,7 +133,7 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
         return (mt & META_TAG_MASK) == tag;
     }
     const S *tab = reinterpret_cast<const S *>(T.slots);
-    u64 s = slot_hash(lo, KW == 1 ? 0 : hi, idx) & T.mask;
+    u64 s = home;
     for (u32 probes = 0; probes < STORE_MAX_PROBE;) {
         const S *p = tab + s;
         bool match;
@@ -153,8 +153,8 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
             if (t == 0) continue;
             if (t == tag) { slot_out = s; meta_out = mt; return true; }
         }
-        s = (s + 1) & T.mask;
         probes++;
+        s = probe_slot(home, lo, KW == 1 ? 0 : hi, idx, probes, T.mask);
     }
     return false;
 }
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
         const u64 ri = r0 + lane;
         u64 w[RW];
         int n = 0, idx0 = 0;
-        u64 bucket = 0, occ = 0;
+        u64 bucket = 0, occ = 0, gbase = 0;
         if (ri < n_recs) {
             const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(recs + ri * RW);
 #pragma unroll
@@ -216,6 +216,8 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
             }
             rec_unpack_header(P, w[RW - 1], bucket, n, idx0);
             w[RW - 1] &= top_mask;
+            // the minimizer m-mer of the record (nucleotides [idx0, idx0+m) of its first k-mer) places the whole superkmer
+            gbase = group_base(mw_extract64<RW, 3>(w, 2 * (n - 1 + idx0)) & P.m_mask);
             if (O.rec_occ) occ = O.rec_occ[ri];
         } else {
 #pragma unroll
@@ -244,6 +246,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
             const int s_idx0 = __shfl_sync(0xffffffffu, idx0, src_l);
             const u64 s_bucket = __shfl_sync(0xffffffffu, bucket, src_l);
             const u64 s_occ = __shfl_sync(0xffffffffu, occ, src_l);
+            const u64 s_gbase = __shfl_sync(0xffffffffu, gbase, src_l);
             u64 pw[RW];
 #pragma unroll
             for (int i = 0; i < RW; i++) pw[i] = __shfl_sync(0xffffffffu, w[i], src_l);
@@ -252,10 +255,11 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                 u64 lo, hi;
                 record_kmer<RW, KW>(P, pw, s_n, j, lo, hi);
                 const u32 idx = (u32)(s_idx0 + j);
+                const u64 home = (s_gbase + idx) & T.mask;
                 u64 slot = ~0ull;
                 if (MODE == MODE_GET) {
                     u32 mt = 0;
-                    bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
+                    bool found = store_find<KW>(T, lo, hi, idx, home, slot, mt);
                     if (found) { agg_hits++; agg_sum += mt >> 24; }
                     if (O.rec_occ) {
                         u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
@@ -269,7 +273,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                     }
                 } else {
                     const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
-                    int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+                    int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
                     if (res == 1) {
                         new_keys++;
                         if (j == 0) new_recs++;
@@ -318,10 +322,11 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
         {
             u64 lo = kmers[i].lo & P.kmask_lo, hi = kmers[i].hi & P.kmask_hi;
             u32 idx = kmers[i].idx;
+            const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & T.mask;
             u64 slot = ~0ull;
             if (MODE == MODE_GET) {
                 u32 mt = 0;
-                bool found = store_find<KW>(T, lo, hi, idx, slot, mt);
+                bool found = store_find<KW>(T, lo, hi, idx, home, slot, mt);
                 if (slots) slots[i] = found ? slot : ~0ull;
                 if (flags) flags[i] = found;
                 if (data) {
@@ -330,7 +335,7 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
                 }
             } else {
                 const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
-                int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+                int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
                 if (res == 1) {
                     new_keys++;
                     store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
@@ -355,7 +360,8 @@ __global__ void __launch_bounds__(256) replay_kernel(const BriskParams P, const 
         u64 lo = parked[3 * i], hi = parked[3 * i + 1], x = parked[3 * i + 2];
         u32 idx = (u32)(x & 0xFF), add = (u32)(x >> 8);
         u64 slot;
-        int res = store_upsert<KW>(T, lo, hi, idx, add, slot);
+        const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & T.mask;
+        int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
         if (res == 1) {
             atomicAdd(T.counters + 0, 1ull);
             store_note_new(T, bucket_of_kmer(P, lo, hi, (int)idx));
@@ -367,7 +373,7 @@ __global__ void __launch_bounds__(256) replay_kernel(const BriskParams P, const 
 
 // rehash: every occupied slot of `from` is re-seated in `to` with its meta / aux / DATA
 template <int KW>
-__global__ void __launch_bounds__(256) rehash_kernel(StoreView from, StoreView to) {
+__global__ void __launch_bounds__(256) rehash_kernel(const BriskParams P, StoreView from, StoreView to) {
     typedef typename SlotOf<KW>::type S;
     const S *src = reinterpret_cast<const S *>(from.slots);
     S *dst = reinterpret_cast<S *>(to.slots);
@@ -377,8 +383,9 @@ __global__ void __launch_bounds__(256) rehash_kernel(StoreView from, StoreView t
         u64 hi = KW == 2 ? reinterpret_cast<const u64 *>(&v)[1] : 0;
         if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) continue;
         u32 idx = (v.meta & META_TAG_MASK) - 1;
-        u64 s = slot_hash(lo, hi, idx) & to.mask;
-        for (;;) {
+        const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & to.mask;
+        u64 s = home;
+        for (u32 probes = 0;;) {
             S *p = dst + s;
             bool won;
             if (KW == 1) {
@@ -395,7 +402,8 @@ __global__ void __launch_bounds__(256) rehash_kernel(StoreView from, StoreView t
                 if (from.data) for (u32 q = 0; q < from.data_size; q++) to.data[s * to.data_size + q] = from.data[i * from.data_size + q];
                 break;
             }
-            s = (s + 1) & to.mask;
+            probes++;
+            s = probe_slot(home, lo, hi, idx, probes, to.mask);
         }
     }
 }
