@@ -1,9 +1,9 @@
 #!/bin/bash
-# ncu evidence for one bench configuration (small genome so that replays stay cheap)
-set -x
+# ncu evidence for one bench configuration (small genome so that replays stay cheap).  usage: scripts/prof1.sh <tag>
+TAG=${1:-r1}
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --skip-e2e --genome 10000000"
-$CMD > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err || exit 1
-cat gpurun_out/prof_plain.json
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'enumerate_kernel|records_kernel' -s 8 -c 4 -o gpurun_out/prof_r1 -f $CMD > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/ncu_full.log
+$CMD > gpurun_out/prof_plain_$TAG.json 2> gpurun_out/prof_plain_$TAG.err || exit 1
+cat gpurun_out/prof_plain_$TAG.json
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launch_$TAG.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'enumerate_kernel|records_kernel' -s 8 -c 4 -o gpurun_out/prof_$TAG -f $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
+tail -3 gpurun_out/ncu_full_$TAG.log
