@@ -180,7 +180,7 @@ def run_ours(args):
     hint = 2 * GENOME + (1 << 20)  # k > 32: about 1.93 stored keys per genomic k-mer
 
     def make_index():
-        idx = Brisk(Parameters(K, M, B), capacity_hint=hint)
+        idx = Brisk(Parameters(K, M, B), capacity_hint=hint if world == 1 else int(hint * 1.1 / world), device=local)
         idx.set_stream(stream.cuda_stream)
         if world > 1:
             idx.comm_init_torch(dist, rank, world)

@@ -26,6 +26,11 @@ PROTOTYPES = {
     "brisk_sync": (C.c_int, [C.c_void_p]),
     "brisk_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]),
+    "brisk_partition_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint64,
+                                        C.c_void_p, C.POINTER(C.c_uint32)]),
+    "brisk_apply_records": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "brisk_comm_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "brisk_exchange_plan": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "brisk_comm_unique_id": (C.c_int, [C.c_void_p]),
     "brisk_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "brisk_owner_of_bucket": (C.c_uint32, [C.c_uint64, C.c_uint8, C.c_uint32]),

@@ -63,6 +63,13 @@ class Brisk:
         self.params = params
         self.data_size = data_size
         self._lib = _capi.load()
+        if device < 0:
+            # the library links its own CUDA runtime, whose "current device" is not torch's: follow torch when the
+            # caller has selected a device there (torch.cuda.set_device), else device 0
+            import sys
+            torch = sys.modules.get("torch")
+            device = torch.cuda.current_device() if torch is not None and torch.cuda.is_initialized() else 0
+        self.device = device
         h = C.c_void_p()
         rc = self._lib.brisk_create(params.k, params.m, params.b, data_size, device, capacity_hint, flags, C.byref(h))
         self._h = h if rc == 0 else None
@@ -128,6 +135,53 @@ class Brisk:
         self._check(self._lib.brisk_query_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), C.byref(hits), C.byref(total)))
         return hits.value, total.value
 
+    # ---- the two halves of the routed path (multi-GPU building blocks)
+    def partition_reads(self, bases, offsets, n_ranks):
+        """(records grouped by owner rank, starts[n_ranks + 1]) — what a rank sends in the exchange."""
+        n = self._n_reads(offsets)
+        starts = np.zeros(n_ranks + 1, np.uint64)
+        rw = C.c_uint32()
+        self._check(self._lib.brisk_partition_reads(self._h, _ptr(bases), _ptr(offsets), n, n_ranks, None, 0, _ptr(starts), C.byref(rw)))
+        recs = np.zeros((int(starts[-1]), rw.value), np.uint64)
+        if len(recs):
+            self._check(self._lib.brisk_partition_reads(self._h, _ptr(bases), _ptr(offsets), n, n_ranks, _ptr(recs), len(recs),
+                                                        _ptr(starts), C.byref(rw)))
+        return recs, starts
+
+    def apply_records(self, recs, op="count"):
+        """Insert / count / look up superkmer records on this handle; returns (hits, total) for op='get'."""
+        code = {"count": 0, "insert": 1, "get": 2}[op]
+        hits, total = C.c_uint64(), C.c_uint64()
+        n = recs.shape[0]
+        self._check(self._lib.brisk_apply_records(self._h, _ptr(recs) if n else None, n, code, C.byref(hits), C.byref(total)))
+        return hits.value, total.value
+
+    # ---- sharded index: one process per GPU
+    def comm_init(self, unique_id, rank, n_ranks):
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+        self._check(self._lib.brisk_comm_init(self._h, buf, rank, n_ranks))
+
+    def comm_unique_id(self):
+        buf = (C.c_uint8 * 128)()
+        self._check(self._lib.brisk_comm_unique_id(buf))
+        return bytes(buf)
+
+    def comm_init_torch(self, dist, rank, n_ranks):
+        """Bootstraps the library's NCCL communicator over an initialised torch.distributed group."""
+        import torch
+        dev = torch.device("cuda") if dist.get_backend() == "nccl" else torch.device("cpu")
+        t = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            t = torch.frombuffer(bytearray(self.comm_unique_id()), dtype=torch.uint8).clone()
+        t = t.to(dev)
+        dist.broadcast(t, src=0)
+        self.comm_init(t.cpu().numpy().tobytes(), rank, n_ranks)
+
+    def comm_info(self):
+        r, n = C.c_int(), C.c_int()
+        self._check(self._lib.brisk_comm_info(self._h, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
     def set_stream(self, cuda_stream):
         self._check(self._lib.brisk_set_stream(self._h, C.c_void_p(cuda_stream)))
 
@@ -186,6 +240,21 @@ class Brisk:
         n = C.c_uint32()
         self._check(self._lib.brisk_last_timing(self._h, ms, C.byref(n)))
         return dict(pack_ms=ms[0], enumerate_ms=ms[1], partition_ms=ms[2], store_ms=ms[3], total_ms=ms[4], launches=n.value)
+
+
+def owner_of_bucket(bucket_id, b, n_ranks):
+    return _capi.load().brisk_owner_of_bucket(int(bucket_id), int(b), int(n_ranks))
+
+
+def exchange_plan(counts, rank):
+    """(send_start, recv_start) of `rank` from the n x n matrix of record counts (row = sender)."""
+    counts = np.ascontiguousarray(counts, dtype=np.uint64)
+    n = counts.shape[0]
+    ss, rs = np.zeros(n + 1, np.uint64), np.zeros(n + 1, np.uint64)
+    rc = _capi.load().brisk_exchange_plan(_ptr(counts), n, rank, _ptr(ss), _ptr(rs))
+    if rc:
+        raise BriskError("brisk_exchange_plan: %d" % rc)
+    return ss, rs
 
 
 def decode_records(recs, params):

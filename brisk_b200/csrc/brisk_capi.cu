@@ -14,7 +14,9 @@
 #include "../../include/brisk_b200.h"
 #include "common.cuh"
 #include "enumerate.cuh"
+#include "partition.cuh"
 #include "store.cuh"
+#include "comm.cuh"
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) {
@@ -74,6 +76,10 @@ struct brisk_handle {
     // scratch
     DevBuf d_bases, d_offsets, d_packed, d_recs, d_rec_occ, d_kmer_base, d_cnt, d_out_slots, d_out_flags, d_out_data,
         d_kmers, d_cub;
+    // partition / exchange (sharded index and the partition entry point)
+    DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
+    u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
+    Comm *comm = nullptr;
     uint64_t *d_rec_count = nullptr;  // device counter
     std::mutex mu;
 };
@@ -236,6 +242,7 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
     CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
+    CK(cudaMalloc((void **)&h->d_part, (64 + 65 + 64 + 64 * 64 + 7) * sizeof(uint64_t)));
     if (flags & BRISK_F_MANAGED) CK(cudaMallocManaged((void **)&h->special, 64 * sizeof(uint32_t)));
     else CK(cudaMalloc((void **)&h->special, 64 * sizeof(uint32_t)));
     CK(cudaMemsetAsync(h->special, 0, 64 * sizeof(uint32_t), h->stream));
@@ -257,8 +264,14 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf *bufs[] = {&h->d_bases, &h->d_offsets, &h->d_packed, &h->d_recs, &h->d_rec_occ, &h->d_kmer_base, &h->d_cnt,
-                      &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub};
+                      &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_send, &h->d_send_occ,
+                      &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data};
     for (DevBuf *b : bufs) b->release();
+    if (h->comm) {
+        if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
+        delete h->comm;
+    }
+    cudaFree(h->d_part);
     cudaFree(h->slots);
     cudaFree(h->data);
     cudaFree(h->special);
@@ -382,31 +395,243 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
 }
 
 template <int RW, int KW, int MODE>
-static cudaError_t launch_records_t(brisk_handle *h, uint64_t n_recs, OccOut O) {
+static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n_recs, OccOut O) {
     if (n_recs == 0) return cudaSuccess;
     uint64_t want = (n_recs + 255) / 256;  // one warp per 32 records
     unsigned blocks = (unsigned)std::min<uint64_t>(want, 148 * 8 * 4);
-    records_kernel<RW, KW, MODE><<<blocks, 256, 0, h->stream>>>(h->P, (const u64 *)h->d_recs.p, n_recs, view_of(h), O);
+    records_kernel<RW, KW, MODE><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, view_of(h), O);
     return cudaGetLastError();
 }
 template <int RW, int KW>
-static cudaError_t launch_records_m(brisk_handle *h, int mode, uint64_t n_recs, OccOut O) {
+static cudaError_t launch_records_m(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O) {
     switch (mode) {
-        case MODE_COUNT: return launch_records_t<RW, KW, MODE_COUNT>(h, n_recs, O);
-        case MODE_INSERT: return launch_records_t<RW, KW, MODE_INSERT>(h, n_recs, O);
-        default: return launch_records_t<RW, KW, MODE_GET>(h, n_recs, O);
+        case MODE_COUNT: return launch_records_t<RW, KW, MODE_COUNT>(h, recs, n_recs, O);
+        case MODE_INSERT: return launch_records_t<RW, KW, MODE_INSERT>(h, recs, n_recs, O);
+        default: return launch_records_t<RW, KW, MODE_GET>(h, recs, n_recs, O);
     }
 }
-static cudaError_t launch_records(brisk_handle *h, int mode, uint64_t n_recs, OccOut O) {
+static cudaError_t launch_records(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O) {
     const int RW = h->P.rec_words, KW = h->P.key_words;
     if (KW == 1) {
-        if (RW == 2) return launch_records_m<2, 1>(h, mode, n_recs, O);
-        if (RW == 4) return launch_records_m<4, 1>(h, mode, n_recs, O);
-        return launch_records_m<6, 1>(h, mode, n_recs, O);
+        if (RW == 2) return launch_records_m<2, 1>(h, mode, recs, n_recs, O);
+        if (RW == 4) return launch_records_m<4, 1>(h, mode, recs, n_recs, O);
+        return launch_records_m<6, 1>(h, mode, recs, n_recs, O);
     }
-    if (RW == 2) return launch_records_m<2, 2>(h, mode, n_recs, O);
-    if (RW == 4) return launch_records_m<4, 2>(h, mode, n_recs, O);
-    return launch_records_m<6, 2>(h, mode, n_recs, O);
+    if (RW == 2) return launch_records_m<2, 2>(h, mode, recs, n_recs, O);
+    if (RW == 4) return launch_records_m<4, 2>(h, mode, recs, n_recs, O);
+    return launch_records_m<6, 2>(h, mode, recs, n_recs, O);
+}
+
+// ------------------------------------------------------------------------------------------------ partition / exchange
+#define NCK(call)                                                                                                     \
+    do {                                                                                                              \
+        ncclResult_t r_ = (call);                                                                                     \
+        if (r_ != ncclSuccess)                                                                                        \
+            return fail(BRISK_E_COMM, std::string(#call) + ": " + g_nccl.GetErrorString(r_) + " (" + __FILE__ + ":" + \
+                                          std::to_string(__LINE__) + ")");                                            \
+    } while (0)
+
+static u64 *part_totals(brisk_handle *h) { return h->d_part; }
+static u64 *part_starts(brisk_handle *h) { return h->d_part + 64; }
+static u64 *part_cursors(brisk_handle *h) { return h->d_part + 64 + 65; }
+static u64 *part_matrix(brisk_handle *h) { return h->d_part + 64 + 65 + 64; }
+
+template <int RW>
+static cudaError_t launch_partition(brisk_handle *h, uint64_t n_recs, uint32_t n_ranks, bool with_occ) {
+    const int shift = 64 - 2 * h->P.b;
+    const u64 *recs = (const u64 *)h->d_recs.p;
+    unsigned b1 = (unsigned)std::min<uint64_t>((n_recs + PART_THREADS - 1) / PART_THREADS, 148 * 8);
+    partition_count_kernel<RW><<<b1, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_totals(h));
+    partition_starts_kernel<<<1, 32, 0, h->stream>>>(part_totals(h), n_ranks, part_starts(h), part_cursors(h));
+    unsigned b2 = (unsigned)std::min<uint64_t>((n_recs + PART_TILE - 1) / PART_TILE, 148 * 4);
+    partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_cursors(h), (u64 *)h->d_send.p,
+                                                                      with_occ ? (const u64 *)h->d_rec_occ.p : nullptr,
+                                                                      with_occ ? (u64 *)h->d_send_occ.p : nullptr);
+    return cudaGetLastError();
+}
+
+// d_recs (+ d_rec_occ) -> d_send (+ d_send_occ), one contiguous region per destination rank; the per-destination
+// totals and region starts stay on the device (part_totals / part_starts)
+static int partition_batch(brisk_handle *h, uint64_t n_recs, uint32_t n_ranks, bool with_occ) {
+    const int RW = h->P.rec_words;
+    CK(cudaMemsetAsync(part_totals(h), 0, 64 * sizeof(uint64_t), h->stream));
+    CK(h->d_send.ensure((n_recs + 1) * RW * sizeof(uint64_t)));
+    if (with_occ) CK(h->d_send_occ.ensure((n_recs + 1) * sizeof(uint64_t)));
+    if (n_recs == 0) {
+        partition_starts_kernel<<<1, 32, 0, h->stream>>>(part_totals(h), n_ranks, part_starts(h), part_cursors(h));
+        CK(cudaGetLastError());
+        h->last_launches += 1;
+        return BRISK_OK;
+    }
+    CK(RW == 2 ? launch_partition<2>(h, n_recs, n_ranks, with_occ)
+               : RW == 4 ? launch_partition<4>(h, n_recs, n_ranks, with_occ) : launch_partition<6>(h, n_recs, n_ranks, with_occ));
+    h->last_launches += 3;
+    return BRISK_OK;
+}
+
+// number of k-mers of every record -> exclusive prefix (n_recs + 1 entries) in `off`
+template <int RW>
+__global__ void __launch_bounds__(256) rec_n_kernel(const BriskParams P, const u64 *__restrict__ recs, u64 n_recs, u64 *__restrict__ n_out) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_recs) return;
+    u64 n = 0;
+    if (i < n_recs) {
+        u64 bucket;
+        int nn, idx0;
+        rec_unpack_header(P, recs[i * RW + (RW - 1)], bucket, nn, idx0);
+        n = (u64)nn;
+    }
+    n_out[i] = n;
+}
+static int occurrence_offsets(brisk_handle *h, const u64 *recs, uint64_t n_recs, DevBuf &off) {
+    const int RW = h->P.rec_words;
+    CK(h->d_cnt.ensure((n_recs + 1) * sizeof(uint64_t)));
+    CK(off.ensure((n_recs + 1) * sizeof(uint64_t)));
+    unsigned blocks = (unsigned)((n_recs + 1 + 255) / 256);
+    if (RW == 2) rec_n_kernel<2><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, (u64 *)h->d_cnt.p);
+    else if (RW == 4) rec_n_kernel<4><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, (u64 *)h->d_cnt.p);
+    else rec_n_kernel<6><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, (u64 *)h->d_cnt.p);
+    CK(cudaGetLastError());
+    size_t tmp = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, (u64 *)h->d_cnt.p, (u64 *)off.p, (int)(n_recs + 1), h->stream));
+    CK(h->d_cub.ensure(tmp));
+    CK(cub::DeviceScan::ExclusiveSum(h->d_cub.p, tmp, (u64 *)h->d_cnt.p, (u64 *)off.p, (int)(n_recs + 1), h->stream));
+    h->last_launches += 3;
+    return BRISK_OK;
+}
+
+// owner side: results of record i go to [off[i], off[i] + n) in emission order
+__global__ void __launch_bounds__(256) occ_tag_kernel(const u64 *off, u64 n_recs, u64 *tag) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_recs) tag[i] = off[i] << 1;
+}
+
+// source side: the results that came back (send order, emission order inside a record) -> read order
+template <int RW>
+__global__ void __launch_bounds__(256) scatter_results_kernel(const BriskParams P, const u64 *__restrict__ send_recs,
+                                                              const u64 *__restrict__ send_occ, const u64 *__restrict__ off,
+                                                              u64 n_recs, const u64 *__restrict__ starts, u32 n_ranks,
+                                                              const u64 *__restrict__ back_slots, const unsigned char *__restrict__ back_flags,
+                                                              const unsigned char *__restrict__ back_data, u32 data_size, u64 *slots,
+                                                              unsigned char *flags, unsigned char *data) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_recs) return;
+    u64 bucket;
+    int n, idx0;
+    rec_unpack_header(P, send_recs[i * RW + (RW - 1)], bucket, n, idx0);
+    u32 d = 0;
+    while (d + 1 < n_ranks && starts[d + 1] <= i) d++;
+    const u64 tag = send_occ[i], o = off[i];
+    for (int j = 0; j < n; j++) {
+        const u64 oi = (tag >> 1) + ((tag & 1) ? (u64)(n - 1 - j) : (u64)j);
+        if (flags) flags[oi] = back_flags[o + j];
+        if (slots) {
+            u64 sl = back_slots[o + j];
+            slots[oi] = sl == ~0ull ? sl : (sl | ((u64)d << 56));  // slot ids of a sharded index carry the owner rank
+        }
+        if (data) for (u32 q = 0; q < data_size; q++) data[oi * data_size + q] = back_data[(o + j) * data_size + q];
+    }
+}
+
+// sharded index: partitions the enumerated records of this rank, exchanges them all-to-all and returns the records
+// this rank owns (d_recv).  With per-occurrence outputs the plan of the way back is prepared too.
+struct Exchange {
+    const u64 *recs = nullptr;   // records to insert / look up here
+    uint64_t n = 0;
+    std::vector<uint64_t> send_occ_start, recv_occ_start;  // occurrence offsets at the region boundaries (with_occ)
+};
+
+static int exchange_records(brisk_handle *h, uint64_t n_recs, bool with_occ, Exchange &X) {
+    Comm &c = *h->comm;
+    const int RW = h->P.rec_words, n = c.n;
+    int rc = partition_batch(h, n_recs, (uint32_t)n, with_occ);
+    if (rc) return rc;
+    NCK(g_nccl.AllGather(part_totals(h), part_matrix(h), (size_t)n, ncclUint64, c.comm, h->stream));
+    c.h_matrix.resize((size_t)n * n);
+    CK(cudaMemcpyAsync(c.h_matrix.data(), part_matrix(h), (size_t)n * n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    if (with_occ) {
+        rc = occurrence_offsets(h, (const u64 *)h->d_send.p, n_recs, h->d_occ_off);
+        if (rc) return rc;
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    c.send_start.assign(n + 1, 0);
+    c.recv_start.assign(n + 1, 0);
+    exchange_plan(c.h_matrix.data(), n, c.rank, c.send_start.data(), c.recv_start.data());
+    if (c.send_start[n] != n_recs) return fail(BRISK_E_COMM, "partition lost records");
+    const uint64_t n_recv = c.recv_start[n];
+    CK(h->d_recv.ensure((n_recv + 1) * RW * sizeof(uint64_t)));
+    NCK(g_nccl.GroupStart());
+    for (int p = 0; p < n; p++) {
+        uint64_t sc = c.send_start[p + 1] - c.send_start[p], rcnt = c.recv_start[p + 1] - c.recv_start[p];
+        if (sc) NCK(g_nccl.Send((const u64 *)h->d_send.p + c.send_start[p] * RW, sc * RW, ncclUint64, p, c.comm, h->stream));
+        if (rcnt) NCK(g_nccl.Recv((u64 *)h->d_recv.p + c.recv_start[p] * RW, rcnt * RW, ncclUint64, p, c.comm, h->stream));
+    }
+    NCK(g_nccl.GroupEnd());
+    X.recs = (const u64 *)h->d_recv.p;
+    X.n = n_recv;
+    if (with_occ) {
+        rc = occurrence_offsets(h, X.recs, n_recv, h->d_recv_occ);  // d_recv_occ first holds the offsets ...
+        if (rc) return rc;
+        X.send_occ_start.assign(n + 1, 0);
+        X.recv_occ_start.assign(n + 1, 0);
+        for (int p = 0; p <= n; p++) {
+            CK(cudaMemcpyAsync(&X.send_occ_start[p], (u64 *)h->d_occ_off.p + c.send_start[p], sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaMemcpyAsync(&X.recv_occ_start[p], (u64 *)h->d_recv_occ.p + c.recv_start[p], sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        }
+        if (n_recv) {  // ... then the tags the store kernel reads (offset << 1: emission order, contiguous)
+            occ_tag_kernel<<<(unsigned)((n_recv + 255) / 256), 256, 0, h->stream>>>((const u64 *)h->d_recv_occ.p, n_recv, (u64 *)h->d_recv_occ.p);
+            CK(cudaGetLastError());
+            h->last_launches++;
+        }
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return BRISK_OK;
+}
+
+// the way back of per-occurrence results: owner-side arrays (d_ret_*) -> source-side arrays in send order
+// (d_out_* are the caller-order staging buffers, so the send-order copies live in d_cnt-independent buffers)
+static int return_results(brisk_handle *h, const Exchange &X, uint64_t n_recs, bool want_slots, bool want_flags, bool want_data,
+                          DevBuf &back_slots, DevBuf &back_flags, DevBuf &back_data, u64 *o_slots, unsigned char *o_flags,
+                          unsigned char *o_data) {
+    Comm &c = *h->comm;
+    const int n = c.n;
+    const uint64_t n_back = X.send_occ_start[n];
+    const uint32_t ds = h->data_size;
+    if (want_slots) CK(back_slots.ensure((n_back + 1) * 8));
+    if (want_flags) CK(back_flags.ensure(n_back + 1));
+    if (want_data) CK(back_data.ensure((n_back + 1) * ds));
+    NCK(g_nccl.GroupStart());
+    for (int p = 0; p < n; p++) {
+        uint64_t sc = X.recv_occ_start[p + 1] - X.recv_occ_start[p], so = X.recv_occ_start[p];
+        uint64_t rcnt = X.send_occ_start[p + 1] - X.send_occ_start[p], ro = X.send_occ_start[p];
+        if (want_slots) {
+            if (sc) NCK(g_nccl.Send((const u64 *)h->d_ret_slots.p + so, sc, ncclUint64, p, c.comm, h->stream));
+            if (rcnt) NCK(g_nccl.Recv((u64 *)back_slots.p + ro, rcnt, ncclUint64, p, c.comm, h->stream));
+        }
+        if (want_flags) {
+            if (sc) NCK(g_nccl.Send((const char *)h->d_ret_flags.p + so, sc, ncclUint8, p, c.comm, h->stream));
+            if (rcnt) NCK(g_nccl.Recv((char *)back_flags.p + ro, rcnt, ncclUint8, p, c.comm, h->stream));
+        }
+        if (want_data) {
+            if (sc) NCK(g_nccl.Send((const char *)h->d_ret_data.p + so * ds, sc * ds, ncclUint8, p, c.comm, h->stream));
+            if (rcnt) NCK(g_nccl.Recv((char *)back_data.p + ro * ds, rcnt * ds, ncclUint8, p, c.comm, h->stream));
+        }
+    }
+    NCK(g_nccl.GroupEnd());
+    if (n_recs) {
+        const int RW = h->P.rec_words;
+        unsigned blocks = (unsigned)((n_recs + 255) / 256);
+#define LAUNCH_SC(RWV)                                                                                                              \
+    scatter_results_kernel<RWV><<<blocks, 256, 0, h->stream>>>(h->P, (const u64 *)h->d_send.p, (const u64 *)h->d_send_occ.p,        \
+                                                                (const u64 *)h->d_occ_off.p, n_recs, part_starts(h), (u32)n,        \
+                                                                (const u64 *)back_slots.p, (const unsigned char *)back_flags.p,     \
+                                                                (const unsigned char *)back_data.p, ds, o_slots, o_flags, o_data)
+        if (RW == 2) LAUNCH_SC(2); else if (RW == 4) LAUNCH_SC(4); else LAUNCH_SC(6);
+#undef LAUNCH_SC
+        CK(cudaGetLastError());
+        h->last_launches++;
+    }
+    return BRISK_OK;
 }
 
 // makes room for `incoming` more k-mer occurrences before an insert
@@ -470,45 +695,76 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
     if (rc) return rc;
     CK(cudaEventRecord(h->ev[2], h->stream));
+    const bool sharded = h->comm && h->comm->n > 1;
+    Exchange X;
+    X.recs = (const u64 *)h->d_recs.p;
+    X.n = n_recs;
+    if (sharded) {
+        rc = exchange_records(h, n_recs, with_occ, X);
+        if (rc) return rc;
+    }
     CK(cudaEventRecord(h->ev[3], h->stream));
     if (mode != MODE_GET) {
-        rc = pregrow(h, B.total_bytes);
+        rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes);
         if (rc) return rc;
     }
     OccOut O;
-    O.rec_occ = with_occ ? (const u64 *)h->d_rec_occ.p : nullptr;
-    O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
+    O.rec_occ = nullptr; O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
     if (agg_out) {
         CK(cudaMemsetAsync(h->counters + 5, 0, 2 * sizeof(uint64_t), h->stream));
         O.agg = h->counters + 5;
     }
     // per-occurrence outputs go through device staging when the caller's buffers are on the host
     bool s_dev = is_device_ptr(slots), f_dev = is_device_ptr(flags), d_dev = is_device_ptr(data_out);
+    u64 *o_slots = nullptr;
+    unsigned char *o_flags = nullptr, *o_data = nullptr;
     if (slots) {
-        if (s_dev) O.slots = (u64 *)slots;
-        else { CK(h->d_out_slots.ensure((n_occ + 1) * sizeof(uint64_t))); O.slots = (u64 *)h->d_out_slots.p; }
+        if (s_dev) o_slots = (u64 *)slots;
+        else { CK(h->d_out_slots.ensure((n_occ + 1) * sizeof(uint64_t))); o_slots = (u64 *)h->d_out_slots.p; }
     }
     if (flags) {
-        if (f_dev) O.flags = flags;
-        else { CK(h->d_out_flags.ensure(n_occ + 1)); O.flags = (unsigned char *)h->d_out_flags.p; }
+        if (f_dev) o_flags = flags;
+        else { CK(h->d_out_flags.ensure(n_occ + 1)); o_flags = (unsigned char *)h->d_out_flags.p; }
     }
     if (data_out) {
-        if (d_dev) O.data = (unsigned char *)data_out;
-        else { CK(h->d_out_data.ensure((n_occ + 1) * h->data_size)); O.data = (unsigned char *)h->d_out_data.p; }
+        if (d_dev) o_data = (unsigned char *)data_out;
+        else { CK(h->d_out_data.ensure((n_occ + 1) * h->data_size)); o_data = (unsigned char *)h->d_out_data.p; }
     }
-    CK(launch_records(h, mode, n_recs, O));
-    if (n_recs) h->last_launches++;
+    DevBuf back_slots, back_flags, back_data;
+    if (!sharded) {
+        O.rec_occ = with_occ ? (const u64 *)h->d_rec_occ.p : nullptr;
+        O.slots = o_slots; O.flags = o_flags; O.data = o_data;
+    } else if (with_occ) {
+        // the owner writes its answers in arrival order; they travel back and are put in read order below
+        const uint64_t n_ret = X.recv_occ_start[h->comm->n];
+        O.rec_occ = (const u64 *)h->d_recv_occ.p;
+        if (slots) { CK(h->d_ret_slots.ensure((n_ret + 1) * sizeof(uint64_t))); O.slots = (u64 *)h->d_ret_slots.p; }
+        if (flags) { CK(h->d_ret_flags.ensure(n_ret + 1)); O.flags = (unsigned char *)h->d_ret_flags.p; }
+        if (data_out) { CK(h->d_ret_data.ensure((n_ret + 1) * h->data_size)); O.data = (unsigned char *)h->d_ret_data.p; }
+    }
+    CK(launch_records(h, mode, X.recs, X.n, O));
+    if (X.n) h->last_launches++;
+    if (sharded && with_occ) {
+        rc = return_results(h, X, n_recs, slots != nullptr, flags != nullptr, data_out != nullptr, back_slots, back_flags, back_data,
+                            o_slots, o_flags, o_data);
+        if (rc) return rc;
+    }
+    if (sharded && agg_out)  // every rank gets the totals of the whole query batch
+        NCK(g_nccl.AllReduce(h->counters + 5, h->counters + 5, 2, ncclUint64, ncclSum, h->comm->comm, h->stream));
     CK(cudaEventRecord(h->ev[4], h->stream));
-    if (slots && !s_dev) CK(cudaMemcpyAsync(slots, O.slots, n_occ * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
-    if (flags && !f_dev) CK(cudaMemcpyAsync(flags, O.flags, n_occ, cudaMemcpyDeviceToHost, h->stream));
-    if (data_out && !d_dev) CK(cudaMemcpyAsync(data_out, O.data, n_occ * h->data_size, cudaMemcpyDeviceToHost, h->stream));
+    if (slots && !s_dev) CK(cudaMemcpyAsync(slots, o_slots, n_occ * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    if (flags && !f_dev) CK(cudaMemcpyAsync(flags, o_flags, n_occ, cudaMemcpyDeviceToHost, h->stream));
+    if (data_out && !d_dev) CK(cudaMemcpyAsync(data_out, o_data, n_occ * h->data_size, cudaMemcpyDeviceToHost, h->stream));
     if (agg_out) CK(cudaMemcpyAsync(agg_out, h->counters + 5, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     if (mode != MODE_GET) {
         rc = settle(h);
-        if (rc) return rc;
     } else {
-        CK(cudaStreamSynchronize(h->stream));
+        rc = BRISK_OK;
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) rc = fail(BRISK_E_CUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
     }
+    back_slots.release(); back_flags.release(); back_data.release();
+    if (rc) return rc;
     finish_timing(h);
     return BRISK_OK;
 }
@@ -668,14 +924,20 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&nb, h->counters + 4, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    if (nb_buckets) *nb_buckets = nb;
-    if (nb_skmers) *nb_skmers = h->n_new_recs;
-    if (nb_kmers) *nb_kmers = h->n_keys;
-    if (largest_bucket) *largest_bucket = 0;
-    if (device_bytes) {
-        *device_bytes = h->cap * slot_bytes(h) + h->bitmap_words * 4 + h->ovf_cap * 24 +
-                        (h->data ? (h->cap + 64) * h->data_size : 0);
+    uint64_t v[4] = {nb, h->n_new_recs, h->n_keys,
+                     h->cap * slot_bytes(h) + h->bitmap_words * 4 + h->ovf_cap * 24 + (h->data ? (h->cap + 64) * h->data_size : 0)};
+    if (h->comm && h->comm->n > 1) {  // buckets are disjoint over the ranks: the totals are sums
+        u64 *tmp = part_matrix(h);
+        CK(cudaMemcpyAsync(tmp, v, sizeof(v), cudaMemcpyHostToDevice, h->stream));
+        NCK(g_nccl.AllReduce(tmp, tmp, 4, ncclUint64, ncclSum, h->comm->comm, h->stream));
+        CK(cudaMemcpyAsync(v, tmp, sizeof(v), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
     }
+    if (nb_buckets) *nb_buckets = v[0];
+    if (nb_skmers) *nb_skmers = v[1];
+    if (nb_kmers) *nb_kmers = v[2];
+    if (largest_bucket) *largest_bucket = 0;
+    if (device_bytes) *device_bytes = v[3];
     return BRISK_OK;
 }
 
@@ -715,20 +977,124 @@ extern "C" int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches) 
     return BRISK_OK;
 }
 
-// ---- multi-GPU entry points (filled in by comm.cuh once the exchange step lands)
+// ---- partition and record-level entry points (what a rank does before and after the exchange)
+extern "C" int brisk_partition_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint32_t n_ranks,
+                                     uint64_t *recs, uint64_t cap_recs, uint64_t *starts, uint32_t *rec_words) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_ranks == 0 || n_ranks > PART_MAX_RANKS) return fail(BRISK_E_PARAM, "n_ranks must be 1..64");
+    if (!starts) return fail(BRISK_E_PARAM, "starts is null");
+    std::lock_guard<std::mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    h->last_launches = 0;
+    if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
+    ReadBatch B;
+    int rc = stage_reads(h, bases, offsets, n_reads, B);
+    if (rc) return rc;
+    uint64_t n_recs = 0, n_occ = 0;
+    rc = enumerate_batch(h, B, false, n_recs, n_occ);
+    if (rc) return rc;
+    CK(cudaEventRecord(h->ev[2], h->stream));
+    rc = partition_batch(h, n_recs, n_ranks, false);
+    if (rc) return rc;
+    CK(cudaEventRecord(h->ev[3], h->stream));
+    CK(cudaEventRecord(h->ev[4], h->stream));
+    CK(cudaMemcpyAsync(starts, part_starts(h), (n_ranks + 1) * sizeof(uint64_t),
+                       is_device_ptr(starts) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    if (recs) {
+        if (n_recs > cap_recs) return fail(BRISK_E_CAPACITY, "record buffer too small");
+        CK(cudaMemcpyAsync(recs, h->d_send.p, n_recs * h->P.rec_words * sizeof(uint64_t),
+                           is_device_ptr(recs) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    finish_timing(h);
+    return BRISK_OK;
+}
+
+extern "C" int brisk_apply_records(brisk_t *h, const uint64_t *recs, uint64_t n_recs, int op, uint64_t *hits, uint64_t *total) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_recs && !recs) return fail(BRISK_E_PARAM, "null input");
+    if (op < 0 || op > 2) return fail(BRISK_E_PARAM, "op must be 0 (count), 1 (insert) or 2 (get)");
+    std::lock_guard<std::mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    h->last_launches = 0;
+    const int RW = h->P.rec_words;
+    const u64 *d_r = (const u64 *)recs;
+    if (n_recs && !is_device_ptr(recs)) {
+        CK(h->d_recv.ensure(n_recs * RW * sizeof(uint64_t)));
+        CK(cudaMemcpyAsync(h->d_recv.p, recs, n_recs * RW * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+        d_r = (const u64 *)h->d_recv.p;
+    }
+    for (int i = 0; i < 4; i++) CK(cudaEventRecord(h->ev[i], h->stream));
+    if (op != MODE_GET) {
+        int rc = pregrow(h, n_recs * (uint64_t)h->P.w);
+        if (rc) return rc;
+    }
+    OccOut O;
+    O.rec_occ = nullptr; O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
+    uint64_t agg[2] = {0, 0};
+    if (op == MODE_GET) {
+        CK(cudaMemsetAsync(h->counters + 5, 0, 2 * sizeof(uint64_t), h->stream));
+        O.agg = h->counters + 5;
+    }
+    CK(launch_records(h, op, d_r, n_recs, O));
+    if (n_recs) h->last_launches++;
+    CK(cudaEventRecord(h->ev[4], h->stream));
+    if (op == MODE_GET) {
+        CK(cudaMemcpyAsync(agg, h->counters + 5, sizeof(agg), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    } else {
+        int rc = settle(h);
+        if (rc) return rc;
+    }
+    if (hits) *hits = agg[0];
+    if (total) *total = agg[1];
+    finish_timing(h);
+    return BRISK_OK;
+}
+
+// ---- multi-GPU entry points
 extern "C" uint32_t brisk_owner_of_bucket(uint64_t bucket_id, uint8_t b, uint32_t n_ranks) {
-    // bucket ids are the middle bits of the hashed minimizer; the minimum of a window is biased towards small
-    // hashes, so the id is scrambled before the range split to keep the shards even
     (void)b;
-    uint64_t x = bucket_id * 0x9E3779B97F4A7C15ull;
-    x ^= x >> 32;
-    return (uint32_t)(((x & 0xffffffffull) * n_ranks) >> 32);
+    return owner_of_bucket(bucket_id, n_ranks);
+}
+extern "C" int brisk_exchange_plan(const uint64_t *counts, int n_ranks, int rank, uint64_t *send_start, uint64_t *recv_start) {
+    if (!counts || !send_start || !recv_start || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(BRISK_E_PARAM, "bad argument");
+    exchange_plan(counts, n_ranks, rank, send_start, recv_start);
+    return BRISK_OK;
 }
 extern "C" int brisk_comm_unique_id(uint8_t id[128]) {
-    (void)id;
-    return fail(BRISK_E_COMM, "NCCL exchange not built yet");
+    if (!id) return fail(BRISK_E_PARAM, "null id");
+    if (!g_nccl.load()) return fail(BRISK_E_COMM, g_nccl.error);
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId u;
+    NCK(g_nccl.GetUniqueId(&u));
+    memcpy(id, &u, 128);
+    return BRISK_OK;
 }
 extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int n_ranks) {
-    (void)h; (void)id; (void)rank; (void)n_ranks;
-    return fail(BRISK_E_COMM, "NCCL exchange not built yet");
+    if (!h || !id) return fail(BRISK_E_PARAM, "null argument");
+    if (n_ranks < 1 || n_ranks > PART_MAX_RANKS || rank < 0 || rank >= n_ranks) return fail(BRISK_E_PARAM, "bad rank / n_ranks");
+    if (h->comm) return fail(BRISK_E_PARAM, "the handle already has a communicator");
+    if (h->n_keys) return fail(BRISK_E_PARAM, "brisk_comm_init must come before the first insertion");
+    if (!g_nccl.load()) return fail(BRISK_E_COMM, g_nccl.error);
+    std::lock_guard<std::mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    ncclUniqueId u;
+    memcpy(&u, id, 128);
+    Comm *c = new Comm();
+    c->rank = rank;
+    c->n = n_ranks;
+    ncclResult_t r = g_nccl.CommInitRank(&c->comm, n_ranks, u, rank);
+    if (r != ncclSuccess) {
+        delete c;
+        return fail(BRISK_E_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
+    }
+    h->comm = c;
+    return BRISK_OK;
+}
+extern "C" int brisk_comm_info(brisk_t *h, int *rank, int *n_ranks) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (rank) *rank = h->comm ? h->comm->rank : 0;
+    if (n_ranks) *n_ranks = h->comm ? h->comm->n : 1;
+    return BRISK_OK;
 }

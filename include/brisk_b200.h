@@ -119,12 +119,31 @@ int brisk_set_stream(brisk_t *h, void *stream);
  * device section (ms); n_launches = kernels launched by the call. */
 int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches);
 
+/* ---- the two halves of the routed path, usable on their own.
+ * brisk_partition_reads: enumerate + radix partition of the superkmer records by owner rank, as a rank does
+ * before the exchange (replaces the lock-stripe routing of DenseMenuYo::insert_kmer_vector,
+ * brisk/DenseMenuYo.hpp:248-308).  recs (nullable) receives the records grouped by destination, starts[n_ranks+1]
+ * the first record of every destination's region.
+ * brisk_apply_records: what the owner does with the records it received: op 0 = count (insert + counter update),
+ * 1 = insert, 2 = get (hits / total as brisk_query_reads). */
+int brisk_partition_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint32_t n_ranks,
+                          uint64_t *recs, uint64_t cap_recs, uint64_t *starts, uint32_t *rec_words);
+int brisk_apply_records(brisk_t *h, const uint64_t *recs, uint64_t n_recs, int op, uint64_t *hits, uint64_t *total);
+
 /* ---- multi-GPU: one process per GPU, bucket ids sharded over ranks, superkmers exchanged with NCCL.
- * id = 128 bytes from brisk_comm_unique_id on rank 0, broadcast by the caller. */
+ * id = 128 bytes from brisk_comm_unique_id on rank 0, broadcast by the caller.  After brisk_comm_init the
+ * read-level calls (count / insert / get / query _reads) and brisk_stats are COLLECTIVE: every rank calls them
+ * in the same order, each with its own share of the reads (possibly none).  Per-occurrence outputs come back to
+ * the rank that supplied the read; slot ids carry the owner rank in their top 8 bits.  brisk_dump,
+ * brisk_insert_kmers / brisk_get_kmers and brisk_apply_records stay local to the rank's shard. */
 int brisk_comm_unique_id(uint8_t id[128]);
 int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int n_ranks);
+int brisk_comm_info(brisk_t *h, int *rank, int *n_ranks);
 /* owner rank of a bucket id (pure function; also used by the CPU tests of the routing) */
 uint32_t brisk_owner_of_bucket(uint64_t bucket_id, uint8_t b, uint32_t n_ranks);
+/* send / receive offsets of one exchange from the n x n matrix of record counts (row = sender); both outputs have
+ * n_ranks + 1 entries.  Pure host arithmetic. */
+int brisk_exchange_plan(const uint64_t *counts, int n_ranks, int rank, uint64_t *send_start, uint64_t *recv_start);
 
 const char *brisk_last_error(void);
 const char *brisk_version(void);
