@@ -12,6 +12,8 @@ PROTOTYPES = {
     "brisk_destroy": (C.c_int, [C.c_void_p]),
     "brisk_enumerate_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
+    "brisk_enumerate_reads_tagged": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                               C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.c_void_p]),
     "brisk_count_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
     "brisk_insert_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_get_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),

@@ -106,6 +106,20 @@ class Brisk:
                                                         C.byref(cnt), C.byref(rw)))
         return recs, rw.value
 
+    def enumerate_reads_tagged(self, bases, offsets):
+        """(records, occ) with occ[i] = (first read-order occurrence of record i << 1) | reversed; records sorted by
+        occ >> 1 are in SuperKmerEnumerator::next's emission order."""
+        n = self._n_reads(offsets)
+        cnt, rw = C.c_uint64(), C.c_uint32()
+        self._check(self._lib.brisk_enumerate_reads_tagged(self._h, _ptr(bases), _ptr(offsets), n, None, 0, C.byref(cnt), C.byref(rw), None))
+        recs = np.zeros((cnt.value, rw.value), np.uint64)
+        occ = np.zeros(cnt.value, np.uint64)
+        if cnt.value:
+            self._check(self._lib.brisk_enumerate_reads_tagged(self._h, _ptr(bases), _ptr(offsets), n, _ptr(recs), cnt.value,
+                                                               C.byref(cnt), C.byref(rw), _ptr(occ)))
+        order = np.argsort(occ >> np.uint64(1), kind="stable")
+        return recs[order], occ[order]
+
     def count_reads(self, bases, offsets):
         self._check(self._lib.brisk_count_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets)))
 

@@ -817,6 +817,35 @@ extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64
     return BRISK_OK;
 }
 
+// brisk_enumerate_reads + the read-order tag of every record: occ[i] = (index of the record's first read-order k-mer
+// occurrence << 1) | reversed.  Sorting by occ >> 1 gives SuperKmerEnumerator::next's emission order.
+extern "C" int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *recs,
+                                            uint64_t cap_recs, uint64_t *n_recs_out, uint32_t *rec_words, uint64_t *occ) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    std::lock_guard<std::mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    h->last_launches = 0;
+    if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
+    ReadBatch B;
+    int rc = stage_reads(h, bases, offsets, n_reads, B);
+    if (rc) return rc;
+    uint64_t n_recs = 0, n_occ = 0;
+    rc = enumerate_batch(h, B, true, n_recs, n_occ);
+    if (rc) return rc;
+    for (int i = 2; i <= 4; i++) CK(cudaEventRecord(h->ev[i], h->stream));
+    if (n_recs_out) *n_recs_out = n_recs;
+    if (recs || occ) {
+        if (n_recs > cap_recs) return fail(BRISK_E_CAPACITY, "record buffer too small");
+        if (recs) CK(cudaMemcpyAsync(recs, h->d_recs.p, n_recs * h->P.rec_words * sizeof(uint64_t),
+                                     is_device_ptr(recs) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+        if (occ) CK(cudaMemcpyAsync(occ, h->d_rec_occ.p, n_recs * sizeof(uint64_t),
+                                    is_device_ptr(occ) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    finish_timing(h);
+    return BRISK_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 static int run_kmers(brisk_handle *h, const brisk_kmer *kmers, uint64_t n, int mode, uint64_t *slots, uint8_t *flags,
                      void *data_out) {

@@ -66,6 +66,12 @@ int brisk_destroy(brisk_t *h);
 int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
                           uint64_t *recs, uint64_t cap_recs, uint64_t *n_recs, uint32_t *rec_words);
 
+/* The same, plus the read-order tag of every record: occ[i] = (index of the record's first k-mer occurrence in read
+ * order << 1) | reversed.  Sorting by occ >> 1 restores SuperKmerEnumerator::next's emission order (the C++ mirror's
+ * SuperKmerEnumerator is built on this call). */
+int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads,
+                                 uint64_t *recs, uint64_t cap_recs, uint64_t *n_recs, uint32_t *rec_words, uint64_t *occ);
+
 /* count_sequence for every read (apps/counter.cpp:231-276): insert_superkmer (brisk/Brisk.hpp:123-147)
  * fused with the counter's update  new -> 1, else ++ (uint8 wrap, apps/counter.cpp:262-269). */
 int brisk_count_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads);

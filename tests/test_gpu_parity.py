@@ -251,3 +251,26 @@ def test_device_resident_inputs():
     assert G.dump_sha(*idx.dump()) == c["dump_sha256"]
     t = idx.last_timing()
     assert t["launches"] >= 3 and t["total_ms"] > 0
+
+
+@pytest.mark.parametrize("name", ["test_fa_k63", "debug_fa_k31", "ties_k63_m21", "synth_cfg3"])
+def test_tagged_enumeration_is_in_reference_order(name):
+    """brisk_enumerate_reads_tagged sorted by its tag = the exact emission order of SuperKmerEnumerator::next."""
+    from brisk_b200 import decode_records
+    from oracle.oracle import Oracle
+    c = G.case(name)
+    reads = G.reads_of(c)[:300]
+    idx = make_index(c)
+    bases, offs = G.flat(reads)
+    recs, occ = idx.enumerate_reads_tagged(bases, offs)
+    got = [tuple(kmers) for _, kmers in decode_records(recs, idx.params)]
+    o = Oracle(c["k"], c["m"], c["b"])
+    want = []
+    for seq in reads:
+        e = o.enumerate(seq)
+        if len(e["lo"]) == 0:
+            continue
+        bounds = np.flatnonzero(np.diff(e["skmer"])) + 1
+        for grp in np.split(np.arange(len(e["lo"])), bounds):
+            want.append(tuple(((int(e["hi"][i]) << 64) | int(e["lo"][i]), int(e["idx"][i])) for i in grp))
+    assert got == want
