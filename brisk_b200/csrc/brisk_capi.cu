@@ -78,6 +78,7 @@ struct brisk_handle {
         d_kmers, d_cub;
     // partition / exchange (sharded index and the partition entry point)
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
+    double2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
     u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
     Comm *comm = nullptr;
     uint64_t *d_rec_count = nullptr;  // device counter
@@ -242,6 +243,25 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
     CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
+    {  // grouped decycling tables: entry (g, v) = sum_j code(nucleotide j of v) * w^(m-1-(3g+j)), positions >= m weigh 0
+        const int groups = (m + 2) / 3;
+        std::vector<double2> tab((size_t)groups * 64);
+        for (int g = 0; g < groups; g++)
+            for (int v = 0; v < 64; v++) {
+                double sr = 0, si = 0;
+                for (int j = 0; j < 3; j++) {
+                    const int pos = 3 * g + j, code = (v >> (2 * j)) & 3;
+                    if (pos >= m) break;
+                    sr += code * h->P.tw_c[m - 1 - pos];
+                    si += code * h->P.tw_s[m - 1 - pos];
+                }
+                tab[(size_t)g * 64 + v] = make_double2(sr, si);
+            }
+        CK(cudaMalloc((void **)&h->dec_tab, tab.size() * sizeof(double2)));
+        CK(cudaMemcpy(h->dec_tab, tab.data(), tab.size() * sizeof(double2), cudaMemcpyHostToDevice));
+        h->P.dec_tab = h->dec_tab;
+        h->P.dec_groups = groups;
+    }
     CK(cudaMalloc((void **)&h->d_part, (64 + 65 + 64 + 64 * 64 + 7) * sizeof(uint64_t)));
     if (flags & BRISK_F_MANAGED) CK(cudaMallocManaged((void **)&h->special, 64 * sizeof(uint32_t)));
     else CK(cudaMalloc((void **)&h->special, 64 * sizeof(uint32_t)));
@@ -272,6 +292,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
         delete h->comm;
     }
     cudaFree(h->d_part);
+    cudaFree(h->dec_tab);
     cudaFree(h->slots);
     cudaFree(h->data);
     cudaFree(h->special);
@@ -333,7 +354,8 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
 
 template <int RW>
 static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, EnumOut out) {
-    size_t smem = ((size_t)h->P.w * ENUM_THREADS + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double);
+    size_t smem = ((size_t)h->P.w * ENUM_THREADS + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double) +
+                  64 * (size_t)h->P.dec_groups * sizeof(double2);
     cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<RW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned blocks = (unsigned)((B.n_reads + ENUM_THREADS - 1) / ENUM_THREADS);

@@ -33,6 +33,11 @@ struct BriskParams {
     double guard;           // |R -/+ eps| below this -> literal recomputation
     double coef[4 * 32];    // DecyclingSet::coef, computed on the host with the same libm (Decycling.cpp:7-13)
     double tw_c[32], tw_s[32];  // cos, sin of 2*pi*q/m
+    // [dec_groups][64] complex partial sums of the decycling weights over groups of 3 nucleotides (device memory,
+    // copied to shared memory by the enumeration kernel): entry (g, v) = sum_{j<3} code(nucleotide j of v) *
+    // w^(m-1-(3g+j)), w = exp(2*pi*i/m); built in brisk_create
+    const double2 *dec_tab;
+    int dec_groups;  // ceil(m / 3)
 };
 
 // ---------------------------------------------------------------- hashing.cpp
@@ -125,6 +130,25 @@ __host__ __device__ __forceinline__ u32 dec_mem_double(const double *coef, doubl
 // bfc_hash_64 (brisk/hashing.cpp:8-19), literal
 __host__ __device__ __forceinline__ u64 bfc_hash_literal(const double *coef, double eps, u64 key, u64 mask, int m) {
     return ((u64)dec_mem_double(coef, eps, key, m) << 62) + bfc_mix(key, mask);
+}
+
+// decycling class of an arbitrary m-mer from the grouped tables: S = sum of the group entries, R = Im(S),
+// R(rot) = Im(w S); whenever either value is within `guard` of a threshold the literal
+// summation decides, so the class is always the one DecyclingSet::memDouble returns.
+__device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double *coef, const double2 *tab, u64 seq) {
+    double Sr = 0, Si = 0;
+    u64 c = seq;
+    for (int g = 0; g < P.dec_groups; g++) {
+        const double2 e = tab[g * 64 + (int)(c & 63)];
+        Sr += e.x;
+        Si += e.y;
+        c >>= 6;
+    }
+    const double R = Si, R2 = fma(Sr, P.rot_s, Si * P.rot_c);
+    if (fabs(fabs(R) - P.eps) < P.guard || fabs(fabs(R2) - P.eps) < P.guard) return dec_mem_double(coef, P.eps, seq, P.m);
+    if (R > P.eps) return R2 < P.eps ? 0u : 2u;
+    if (R < -P.eps) return R2 > -P.eps ? 1u : 2u;
+    return 2u;
 }
 
 // ---------------------------------------------------------------- packed reads

@@ -13,7 +13,7 @@
 #include "common.cuh"
 
 #define ENUM_THREADS 128
-#define ENUM_POOL 2048
+#define ENUM_POOL 512
 #define ENUM_SYNC_STEPS 16
 #define DEC_RESYNC 128
 
@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     u64 *ring = smem;                                  // [w][ENUM_THREADS] order hashes of the last w m-mers
     u64 *pool = ring + (size_t)P.w * ENUM_THREADS;     // [ENUM_POOL] superkmer descriptors
     double *coef = (double *)(pool + ENUM_POOL);       // [4m]
+    double2 *dtab = (double2 *)(coef + 4 * P.m);  // [dec_groups][64] grouped decycling weights (16-byte aligned: 4m doubles)
     __shared__ u32 pool_n;
     __shared__ u32 s_maxL;
     __shared__ u64 s_base;
@@ -146,6 +147,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     rd_id[tid] = rid;
     if (tid == 0) { pool_n = 0; s_maxL = 0; }
     for (int i = tid; i < 4 * m; i += ENUM_THREADS) coef[i] = P.coef[i];
+    for (int i = tid; i < 64 * P.dec_groups; i += ENUM_THREADS) dtab[i] = P.dec_tab[i];
     __syncthreads();
     atomicMax(&s_maxL, L);
     __syncthreads();
@@ -271,7 +273,8 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                             u64 v = s_cur >> (2 * lane);
                             u64 rc = rcbc(v, m);
                             u64 c = v < rc ? v : rc;
-                            nh = bfc_hash_literal(coef, P.eps, c, P.m_mask, m);
+                            const u32 pc = P.literal_decycle ? dec_mem_double(coef, P.eps, c, m) : dec_class_tab(P, coef, dtab, c);
+                            nh = ((u64)pc << 62) + bfc_mix(c, P.m_mask);
                             prv = c != v;
                         }
                     }
