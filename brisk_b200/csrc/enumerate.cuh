@@ -13,8 +13,8 @@
 #include "common.cuh"
 
 #define ENUM_THREADS 128
-#define ENUM_POOL 512
-#define ENUM_SYNC_STEPS 16
+#define ENUM_POOL 384
+#define ENUM_SYNC_STEPS 32
 #define DEC_RESYNC 128
 
 // ---------------------------------------------------------------------------------------------
