@@ -57,6 +57,7 @@ struct brisk_handle {
     uint32_t flags = 0;
     uint32_t data_size = 1;
     uint64_t hint = 0;
+    bool use_ring = true;
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[6] = {};
@@ -237,6 +238,8 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     h->flags = flags;
     h->data_size = data_size;
     h->hint = capacity_hint;
+    h->use_ring = k <= 32;
+    if (const char *e = getenv("BRISK_ENUM_RING")) h->use_ring = atoi(e) != 0;  // development switch
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
@@ -352,15 +355,20 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
     return BRISK_OK;
 }
 
-template <int RW>
-static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, EnumOut out) {
-    size_t smem = ((size_t)h->P.w * ENUM_THREADS + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double) +
+template <int RW, bool RING>
+static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, EnumOut out) {
+    size_t smem = ((RING ? (size_t)h->P.w * ENUM_THREADS : 0) + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double) +
                   64 * (size_t)h->P.dec_groups * sizeof(double2);
-    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<RW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<RW, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned blocks = (unsigned)((B.n_reads + ENUM_THREADS - 1) / ENUM_THREADS);
-    enumerate_kernel<RW><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, B.n_reads, out);
+    enumerate_kernel<RW, RING><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, B.n_reads, out);
     return cudaGetLastError();
+}
+template <int RW>
+static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, EnumOut out) {
+    // k > 32: most window positions of a rescan are recomputed anyway, so the ring only costs shared memory
+    return h->use_ring ? launch_enum_t<RW, true>(h, B, out) : launch_enum_t<RW, false>(h, B, out);
 }
 
 __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *counts) {

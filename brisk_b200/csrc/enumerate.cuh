@@ -115,13 +115,17 @@ __device__ __forceinline__ u64 warp_min64(u64 v) {
 // column and a warp reading one thread's column across slots are both free of bank conflicts
 __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_THREADS + (tid ^ (slot & 31)); }
 
-template <int RW>
+// RING = true : every thread keeps the order hashes of its last w m-mers in a shared-memory ring; a rescan reads them.
+// RING = false: no ring (shared memory: staging pool + tables only, twice the resident warps at k = 63); a rescan
+//               recomputes the hash of every window position from the requester's last 32 bases, which k > 32 has to
+//               do anyway for most positions (the 64-bit truncation of get_minimizer, Q3).
+template <int RW, bool RING>
 __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 n_reads,
                                                                  EnumOut out) {
     extern __shared__ u64 smem[];
-    u64 *ring = smem;                                  // [w][ENUM_THREADS] order hashes of the last w m-mers
-    u64 *pool = ring + (size_t)P.w * ENUM_THREADS;     // [ENUM_POOL] superkmer descriptors
+    u64 *ring = smem;                                  // [w][ENUM_THREADS] order hashes of the last w m-mers (RING only)
+    u64 *pool = ring + (RING ? (size_t)P.w * ENUM_THREADS : 0);  // [ENUM_POOL] superkmer descriptors
     double *coef = (double *)(pool + ENUM_POOL);       // [4m]
     double2 *dtab = (double2 *)(coef + 4 * P.m);  // [dec_groups][64] grouped decycling weights (16-byte aligned: 4m doubles)
     __shared__ u32 pool_n;
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     const u32 maxL = s_maxL;
 
     // rolling state
-    u64 f = 0, r = 0, word = 0, revbits = 0;
+    u64 f = 0, r = 0, word = 0, revbits = 0, hist = 0;  // hist: the last 32 bases (RING = false)
     double Ar = 0, Ai = 0, Br = 0, Bi = 0;
     int rslot = -1;           // ring slot of the newest m-mer (the same for every thread: all reads start at t = 0)
     u64 H = 0;                // mini_hash
@@ -194,6 +198,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                 const u32 leave = (u32)(f >> rshift) & 3u;
                 f = ((f << 2) | code) & P.m_mask;
                 r = (r >> 2) | ((u64)(code ^ 2u) << rshift);
+                if (!RING) hist = (hist << 2) | code;
                 if (!P.literal_decycle) {
                     // A = sum of low code bits * w^q, B = sum of high code bits * w^q over the window
                     double la = (double)(leave & 1u), lb = (double)(leave >> 1);
@@ -234,8 +239,10 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                             cls = dec_mem_double(coef, P.eps, canon, m);
                     }
                     h = ((u64)cls << 62) + bfc_mix(canon, P.m_mask);
-                    ring[ring_at(rslot, tid)] = h;
-                    revbits = (revbits << 1) | (u64)rv;
+                    if (RING) {
+                        ring[ring_at(rslot, tid)] = h;
+                        revbits = (revbits << 1) | (u64)rv;
+                    }
                     if (t + 2 == (u32)k) {
                         need_kk = k - 1;
                     } else if (t + 1 >= (u32)k) {
@@ -254,7 +261,8 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                 const int real_max = kk > 32 ? 32 - m : nmax;
                 const bool has_hi = nmax >= 32;  // positions >= 32 hold the all-A pseudo m-mer (Q3)
                 u64 cur64 = 0;
-                if (need_kk && kk > 32) cur64 = get_bits64(pk, (u64)t - 31);
+                if (!RING) cur64 = hist;
+                else if (need_kk && kk > 32) cur64 = get_bits64(pk, (u64)t - 31);
                 while (req) {
                     const int src = __ffs(req) - 1;
                     req &= req - 1;
@@ -264,13 +272,14 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                     u64 nh = ~0ull;
                     bool prv = false;
                     if (lane <= nmax) {
-                        if (lane <= real_max) {
+                        if (RING && lane <= real_max) {
                             int sl = rslot - lane;
                             if (sl < 0) sl += P.w;
                             nh = ring[ring_at(sl, s_tid)];
                             prv = (s_revbits >> lane) & 1;
                         } else {
-                            u64 v = s_cur >> (2 * lane);
+                            // real m-mer (masked) or the zero-padded top of the truncated k-mer (the mask is a no-op)
+                            u64 v = (s_cur >> (2 * lane)) & P.m_mask;
                             u64 rc = rcbc(v, m);
                             u64 c = v < rc ? v : rc;
                             const u32 pc = P.literal_decycle ? dec_mem_double(coef, P.eps, c, m) : dec_class_tab(P, coef, dtab, c);
