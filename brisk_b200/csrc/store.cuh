@@ -43,6 +43,11 @@ __device__ __forceinline__ void ld_relaxed128(const void *addr, u64 &lo, u64 &hi
     asm volatile("{\n .reg .b128 d;\n ld.relaxed.gpu.global.b128 d, [%2];\n mov.b128 {%0,%1}, d;\n}\n"
                  : "=l"(lo), "=l"(hi) : "l"(addr) : "memory");
 }
+__device__ __forceinline__ u32 ld_relaxed32(const u32 *addr) {
+    u32 v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void cas128(void *addr, u64 clo, u64 chi, u64 slo, u64 shi, u64 &olo, u64 &ohi) {
     asm volatile("{\n .reg .b128 c, s, d;\n mov.b128 c, {%3,%4};\n mov.b128 s, {%5,%6};\n"
                  " atom.global.relaxed.gpu.cas.b128 d, [%2], c, s;\n mov.b128 {%0,%1}, d;\n}\n"
@@ -79,8 +84,13 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
     while (probes < STORE_MAX_PROBE) {
         S *p = tab + s;
         bool match;
+        // key and meta are fetched together (one 32-byte sector, one round trip); `mt` is only trusted when the key
+        // it came with matched, and a zero tag sends the probe back to look again
+        u32 mt;
         if (KW == 1) {
-            u64 cur = ld_cg64(reinterpret_cast<const u64 *>(p));
+            u64 cur, w1;
+            ld_relaxed128(p, cur, w1);
+            mt = (u32)w1;
             if (cur == STORE_EMPTY) {
                 u64 old = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo);
                 if (old == STORE_EMPTY) {
@@ -89,11 +99,13 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
                     return 1;
                 }
                 cur = old;
+                mt = 0;  // somebody else claimed the slot meanwhile: re-read its tag
             }
             match = cur == lo;
         } else {
             u64 clo, chi;
             ld_relaxed128(p, clo, chi);
+            mt = ld_relaxed32(&p->meta);
             if (clo == STORE_EMPTY && chi == STORE_EMPTY) {
                 u64 olo, ohi;
                 cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
@@ -103,11 +115,12 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
                     return 1;
                 }
                 clo = olo; chi = ohi;
+                mt = 0;
             }
             match = clo == lo && chi == hi;
         }
         if (match) {
-            u32 t = ld_cg32(&p->meta) & META_TAG_MASK;
+            u32 t = mt & META_TAG_MASK;
             if (t == 0) continue;  // claimed by another thread, tag not published yet: look again
             if (t == tag) {
                 if (add) atomicAdd(&p->meta, add);
@@ -137,18 +150,21 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
     for (u32 probes = 0; probes < STORE_MAX_PROBE;) {
         const S *p = tab + s;
         bool match;
+        u32 mt;
         if (KW == 1) {
-            u64 cur = ld_cg64(reinterpret_cast<const u64 *>(p));
+            u64 cur, w1;
+            ld_relaxed128(p, cur, w1);
+            mt = (u32)w1;
             if (cur == STORE_EMPTY) return false;
             match = cur == lo;
         } else {
             u64 clo, chi;
             ld_relaxed128(p, clo, chi);
+            mt = ld_relaxed32(&p->meta);
             if (clo == STORE_EMPTY && chi == STORE_EMPTY) return false;
             match = clo == lo && chi == hi;
         }
         if (match) {
-            u32 mt = ld_cg32(&p->meta);
             u32 t = mt & META_TAG_MASK;
             if (t == 0) continue;
             if (t == tag) { slot_out = s; meta_out = mt; return true; }
