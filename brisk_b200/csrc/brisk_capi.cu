@@ -31,6 +31,9 @@ static int fail(int code, const std::string &msg) {
                                           std::to_string(__LINE__) + ")");                                 \
     } while (0)
 
+#define BRISK_MAX_CHUNKS 8
+#define BRISK_MIN_CHUNK_BYTES (8u << 20)
+
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -61,6 +64,8 @@ struct brisk_handle {
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[6] = {};
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t chunk_ev[BRISK_MAX_CHUNKS] = {};
     float last_ms[5] = {0, 0, 0, 0, 0};
     uint32_t last_launches = 0;
     // store
@@ -243,6 +248,8 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
+    CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < BRISK_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&h->chunk_ev[i], cudaEventDisableTiming));
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
     CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
@@ -304,6 +311,8 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaFree(h->overflow);
     cudaFree(h->d_rec_count);
     for (int i = 0; i < 6; i++) cudaEventDestroy(h->ev[i]);
+    for (int i = 0; i < BRISK_MAX_CHUNKS; i++) cudaEventDestroy(h->chunk_ev[i]);
+    cudaStreamDestroy(h->copy_stream);
     cudaStreamDestroy(h->own_stream);
     delete h;
     return BRISK_OK;
@@ -315,7 +324,12 @@ struct ReadBatch {
     const u64 *d_offsets = nullptr;
     u64 *d_packed = nullptr;
     uint64_t n_reads = 0, total_bytes = 0;
+    // host input: the bases arrive in chunks on the copy stream, chunk c = reads [chunk_first[c], chunk_first[c + 1]),
+    // ready when h->chunk_ev[c] has fired; pack + enumerate of chunk c overlap the copy of chunk c + 1
+    std::vector<uint64_t> chunk_first;
+    bool chunk_events = false;
 };
+
 
 // copies (if needed) and packs a batch of reads
 static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, ReadBatch &B) {
@@ -332,43 +346,72 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
         B.d_offsets = (const u64 *)h->d_offsets.p;
     }
     B.total_bytes = total;
+    B.chunk_first.assign(1, 0);
     if (is_device_ptr(bases)) {
         B.d_bases = (const unsigned char *)bases;
+        B.chunk_first.push_back(n_reads);
     } else {
         CK(h->d_bases.ensure(total + 16));
-        CK(cudaMemcpyAsync(h->d_bases.p, bases, total, cudaMemcpyHostToDevice, h->stream));
         B.d_bases = (const unsigned char *)h->d_bases.p;
+        // chunks of about total / 8 bytes on read boundaries (the host offsets are at hand), copied on the copy stream
+        const uint64_t want = std::max<uint64_t>(BRISK_MIN_CHUNK_BYTES, (total + BRISK_MAX_CHUNKS - 1) / BRISK_MAX_CHUNKS);
+        uint64_t first = 0;
+        while (first < n_reads && B.chunk_first.size() < BRISK_MAX_CHUNKS) {
+            // last read whose end stays within `want` bytes of the chunk's start
+            const uint64_t limit = offsets[first] + want;
+            uint64_t lo = first + 1, hi = n_reads;
+            while (lo < hi) {
+                uint64_t mid = (lo + hi + 1) / 2;
+                if (offsets[mid] <= limit) lo = mid; else hi = mid - 1;
+            }
+            first = lo;
+            B.chunk_first.push_back(first);
+        }
+        if (B.chunk_first.back() != n_reads) B.chunk_first.back() = n_reads;
+        if (B.chunk_first.size() == 1) B.chunk_first.push_back(n_reads);
+        B.chunk_events = true;
+        for (size_t c = 0; c + 1 < B.chunk_first.size(); c++) {
+            const uint64_t b0 = offsets[B.chunk_first[c]], b1 = offsets[B.chunk_first[c + 1]];
+            if (b1 > b0) CK(cudaMemcpyAsync((char *)h->d_bases.p + b0, bases + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
+            CK(cudaEventRecord(h->chunk_ev[c], h->copy_stream));
+        }
     }
     uint64_t n_words = total / 32 + n_reads + 8;
     CK(h->d_packed.ensure(n_words * sizeof(uint64_t)));
     B.d_packed = (u64 *)h->d_packed.p;
     CK(cudaEventRecord(h->ev[0], h->stream));
-    if (n_reads) {
-        // tail words that get_bits64 may touch past the last read must be readable; zero the pad
-        CK(cudaMemsetAsync(B.d_packed + (n_words - 8), 0, 8 * sizeof(uint64_t), h->stream));
-        unsigned blocks = (unsigned)((n_reads + 7) / 8);
-        pack_reads_kernel<<<blocks, 256, 0, h->stream>>>(B.d_bases, B.d_offsets, n_reads, B.d_packed);
+    // tail words that get_bits64 may touch past the last read must be readable; zero the pad
+    if (n_reads) CK(cudaMemsetAsync(B.d_packed + (n_words - 8), 0, 8 * sizeof(uint64_t), h->stream));
+    return BRISK_OK;
+}
+
+// 2-bit packing of chunk c of a staged batch (after its bases have arrived)
+static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
+    const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
+    if (B.chunk_events) CK(cudaStreamWaitEvent(h->stream, h->chunk_ev[c], 0));
+    if (r1 > r0) {
+        unsigned blocks = (unsigned)((r1 - r0 + 7) / 8);
+        pack_reads_kernel<<<blocks, 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
         CK(cudaGetLastError());
         h->last_launches++;
     }
-    CK(cudaEventRecord(h->ev[1], h->stream));
     return BRISK_OK;
 }
 
 template <int RW, bool RING>
-static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, EnumOut out) {
+static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
     size_t smem = ((RING ? (size_t)h->P.w * ENUM_THREADS : 0) + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double) +
                   64 * (size_t)h->P.dec_groups * sizeof(double2);
     cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<RW, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    unsigned blocks = (unsigned)((B.n_reads + ENUM_THREADS - 1) / ENUM_THREADS);
-    enumerate_kernel<RW, RING><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, B.n_reads, out);
+    unsigned blocks = (unsigned)((r1 - r0 + ENUM_THREADS - 1) / ENUM_THREADS);
+    enumerate_kernel<RW, RING><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
     return cudaGetLastError();
 }
 template <int RW>
-static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, EnumOut out) {
+static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
     // k > 32: most window positions of a rescan are recomputed anyway, so the ring only costs shared memory
-    return h->use_ring ? launch_enum_t<RW, true>(h, B, out) : launch_enum_t<RW, false>(h, B, out);
+    return h->use_ring ? launch_enum_t<RW, true>(h, B, r0, r1, out) : launch_enum_t<RW, false>(h, B, r0, r1, out);
 }
 
 __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *counts) {
@@ -383,7 +426,10 @@ __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *
 static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, uint64_t &n_recs, uint64_t &n_occ) {
     n_recs = 0;
     n_occ = 0;
-    if (B.n_reads == 0) return BRISK_OK;
+    if (B.n_reads == 0) {
+        CK(cudaEventRecord(h->ev[1], h->stream));
+        return BRISK_OK;
+    }
     const int RW = h->P.rec_words;
     if (with_occ) {
         CK(h->d_cnt.ensure((B.n_reads + 1) * sizeof(uint64_t)));
@@ -412,9 +458,18 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
         out.rec_count = (u64 *)h->d_rec_count;
         out.rec_occ = with_occ ? (u64 *)h->d_rec_occ.p : nullptr;
         out.kmer_base = with_occ ? (const u64 *)h->d_kmer_base.p : nullptr;
-        cudaError_t e = RW == 2 ? launch_enum<2>(h, B, out) : RW == 4 ? launch_enum<4>(h, B, out) : launch_enum<6>(h, B, out);
-        CK(e);
-        h->last_launches++;
+        // chunk by chunk: pack + enumerate of a chunk run while the next chunk's bases are still on their way; the
+        // records of all chunks accumulate behind the same device counter
+        for (size_t c = 0; c + 1 < B.chunk_first.size(); c++) {
+            int prc = pack_chunk(h, B, c);
+            if (prc) return prc;
+            if (c == 0) CK(cudaEventRecord(h->ev[1], h->stream));
+            const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
+            if (r1 == r0) continue;
+            cudaError_t e = RW == 2 ? launch_enum<2>(h, B, r0, r1, out) : RW == 4 ? launch_enum<4>(h, B, r0, r1, out) : launch_enum<6>(h, B, r0, r1, out);
+            CK(e);
+            h->last_launches++;
+        }
         CK(cudaMemcpyAsync(&n_recs, h->d_rec_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
         if (n_recs <= cap) break;

@@ -19,11 +19,11 @@
 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__restrict__ bases,
-                                                         const u64 *__restrict__ offsets, u64 n_reads,
+                                                         const u64 *__restrict__ offsets, u64 read0, u64 read_end,
                                                          u64 *__restrict__ packed) {
     const int lane = threadIdx.x & 31;
-    const u64 r = (u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (r >= n_reads) return;
+    const u64 r = read0 + (u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);  // reads [read0, read_end) of the batch
+    if (r >= read_end) return;
     const u64 beg = offsets[r], end = offsets[r + 1];
     const u64 len = end - beg;
     u64 *out = packed + packed_start(beg, r);
@@ -121,7 +121,7 @@ __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_T
 //               do anyway for most positions (the 64-bit truncation of get_minimizer, Q3).
 template <int RW, bool RING>
 __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
-                                                                 const u64 *__restrict__ offsets, u64 n_reads,
+                                                                 const u64 *__restrict__ offsets, u64 read0, u64 n_reads,
                                                                  EnumOut out) {
     extern __shared__ u64 smem[];
     u64 *ring = smem;                                  // [w][ENUM_THREADS] order hashes of the last w m-mers (RING only)
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int k = P.k, m = P.m;
-    const u64 rid = (u64)blockIdx.x * ENUM_THREADS + tid;
+    const u64 rid = read0 + (u64)blockIdx.x * ENUM_THREADS + tid;  // this launch covers reads [read0, n_reads) of the batch
     u32 L = 0;
     u64 wstart = 0;
     if (rid < n_reads) {
