@@ -195,7 +195,10 @@ def run_ours(args):
         acc["launches"] += t["launches"]
         if j > 0:
             hits, total = idx.query_reads(batches[j - 1], offsets)
-            acc["launches"] += idx.last_timing()["launches"]
+            tq = idx.last_timing()
+            acc["launches"] += tq["launches"]
+            acc["q_enum_ms"] += tq["enumerate_ms"]
+            acc["q_store_ms"] += tq["store_ms"]
             acc["hits"] += hits
 
     def barrier():
@@ -206,7 +209,7 @@ def run_ours(args):
 
     def timed(batches, offsets):
         idx = make_index()
-        acc = dict(store_ms=0.0, enum_ms=0.0, pack_ms=0.0, launches=0, hits=0)
+        acc = dict(store_ms=0.0, enum_ms=0.0, pack_ms=0.0, launches=0, hits=0, q_enum_ms=0.0, q_store_ms=0.0)
         wacc = dict(acc)
         # warm-up on the first batches, then a fresh store for the timed steps
         for j in range(min(warmup, n_batches)):
@@ -232,6 +235,9 @@ def run_ours(args):
             ms = float(tms.item())
         return ms, acc, clocks, st
 
+    probe = make_index()
+    n_recs_batch = probe.count_superkmers(dev_batches[0], offs_dev)  # superkmer records of one batch (roofline bytes)
+    probe.close()
     ms_dev, acc_dev, clocks, st_dev = timed(dev_batches, offs_dev)
     ms_e2e, acc_e2e, _, _ = timed(host_batches, offs_host) if not args.skip_e2e else (float("nan"), None, None, None)
     if rank != 0:
@@ -243,10 +249,31 @@ def run_ours(args):
     value = total_occ / (ms_dev / 1000.0)
     e2e = total_occ / (ms_e2e / 1000.0)
     peak, peak_src = peaks()
-    # dominant kernel = records_kernel (insert/count): algorithmic bytes per launch / CUDA-event duration
+    # Kernels of a step: enumerate_kernel twice (count + query), records_kernel<COUNT> once, records_kernel<GET> once.
+    # The roofline object describes the one with the largest share of the step; the other goes to "roofline_other".
+    # Algorithmic bytes per launch follow SURVEY.md §8(d):
+    #   enumerate: sum of read lengths + per superkmer record 8 + ceil((n + k - 1) / 4) bytes
+    #   insert/count: 18 B per occurrence + 16 B per newly stored k-mer
     new_keys = st_dev["nb_kmers"]
-    alg_bytes = steps * occ_per_batch * INSERT_B_PER_OCC + new_keys * INSERT_B_PER_NEW * steps / (steps + 1)
-    achieved = alg_bytes / (acc_dev["store_ms"] / 1000.0) / 1e9 if acc_dev["store_ms"] > 0 else None
+    ins_bytes = occ_per_batch * INSERT_B_PER_OCC + new_keys * INSERT_B_PER_NEW / (steps + 1)
+    ins_ms = acc_dev["store_ms"] / steps
+    enum_bytes = BATCH_READS * READ_LEN + n_recs_batch * (8 + 0.375) + (occ_per_batch + n_recs_batch * (K - 1)) / 4.0
+    enum_ms = (acc_dev["enum_ms"] + acc_dev["q_enum_ms"]) / (2 * steps)
+
+    def roof(kernel, nbytes, ms, launches_per_step, traffic, note):
+        a = nbytes / (ms / 1000.0) / 1e9 if ms > 0 else None
+        return {"bound": "hbm", "kernel": kernel, "achieved": a, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": (a / peak) if a else None, "traffic": traffic, "algorithmic_bytes_per_launch": nbytes,
+                "ms_per_launch": ms, "launches_per_step": launches_per_step,
+                "share_of_step": launches_per_step * ms / (ms_dev / steps), "note": note}
+
+    r_enum = roof("enumerate_kernel<4,ringless> (pack excluded)", enum_bytes, enum_ms, 2, 0.2959e9,
+                  "issue-bound (81 % issue-active in profiles/r1g_summary.md), not HBM-bound; traffic from the ncu capture "
+                  "of the same 2^20-read batch shape")
+    r_ins = roof("records_kernel<4,2,COUNT> (insert/count)", ins_bytes, ins_ms, 1, None,
+                 "random 32-byte sectors: 65 B of DRAM traffic per occurrence in profiles/r1g_summary.md (12.9 GB per launch on "
+                 "the 10 Mbp profiling genome; not captured at the full 17 GB table)")
+    dominant, other = (r_enum, r_ins) if r_enum["share_of_step"] >= r_ins["share_of_step"] else (r_ins, r_enum)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
         "ms_per_step": ms_dev / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -260,11 +287,9 @@ def run_ours(args):
                 "d2h_bytes_per_step": 32 + 16 + 8 + 8},
         "gpu_launches": acc_dev["launches"],
         "stage_ms_per_step": {"pack": acc_dev["pack_ms"] / steps, "enumerate": acc_dev["enum_ms"] / steps,
-                              "insert": acc_dev["store_ms"] / steps},
-        "roofline": {"bound": "hbm", "kernel": "records_kernel<4,2,COUNT> (insert/count)", "achieved": achieved,
-                     "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": None,
-                     "algorithmic_bytes_per_launch": alg_bytes / steps},
+                              "insert": acc_dev["store_ms"] / steps, "query_enumerate": acc_dev["q_enum_ms"] / steps,
+                              "query_get": acc_dev["q_store_ms"] / steps},
+        "roofline": dominant, "roofline_other": other,
     }
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1

@@ -106,6 +106,13 @@ class Brisk:
                                                         C.byref(cnt), C.byref(rw)))
         return recs, rw.value
 
+    def count_superkmers(self, bases, offsets):
+        """number of superkmer records the batch enumerates to (nothing is copied out)"""
+        cnt, rw = C.c_uint64(), C.c_uint32()
+        self._check(self._lib.brisk_enumerate_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), None, 0,
+                                                    C.byref(cnt), C.byref(rw)))
+        return cnt.value
+
     def enumerate_reads_tagged(self, bases, offsets):
         """(records, occ) with occ[i] = (first read-order occurrence of record i << 1) | reversed; records sorted by
         occ >> 1 are in SuperKmerEnumerator::next's emission order."""
@@ -124,6 +131,8 @@ class Brisk:
         self._check(self._lib.brisk_count_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets)))
 
     def n_occurrences(self, offsets):
+        if hasattr(offsets, "cpu"):
+            offsets = offsets.cpu().numpy()
         lens = np.diff(np.asarray(offsets).astype(np.int64))
         return int(np.maximum(lens - self.params.k + 1, 0).sum())
 

@@ -326,7 +326,7 @@ struct ReadBatch {
     uint64_t n_reads = 0, total_bytes = 0;
     // host input: the bases arrive in chunks on the copy stream, chunk c = reads [chunk_first[c], chunk_first[c + 1]),
     // ready when h->chunk_ev[c] has fired; pack + enumerate of chunk c overlap the copy of chunk c + 1
-    std::vector<uint64_t> chunk_first;
+    std::vector<uint64_t> chunk_first, chunk_byte;  // chunk_byte[c] = byte offset of the chunk's first read
     bool chunk_events = false;
 };
 
@@ -350,6 +350,7 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
     if (is_device_ptr(bases)) {
         B.d_bases = (const unsigned char *)bases;
         B.chunk_first.push_back(n_reads);
+        B.chunk_byte = {0, total};
     } else {
         CK(h->d_bases.ensure(total + 16));
         B.d_bases = (const unsigned char *)h->d_bases.p;
@@ -370,6 +371,7 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
         if (B.chunk_first.back() != n_reads) B.chunk_first.back() = n_reads;
         if (B.chunk_first.size() == 1) B.chunk_first.push_back(n_reads);
         B.chunk_events = true;
+        for (uint64_t f : B.chunk_first) B.chunk_byte.push_back(offsets[f]);
         for (size_t c = 0; c + 1 < B.chunk_first.size(); c++) {
             const uint64_t b0 = offsets[B.chunk_first[c]], b1 = offsets[B.chunk_first[c + 1]];
             if (b1 > b0) CK(cudaMemcpyAsync((char *)h->d_bases.p + b0, bases + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
@@ -423,9 +425,11 @@ __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *
 }
 
 // enumerates a staged batch into h->d_recs; with_occ also fills d_rec_occ / d_kmer_base
-static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, uint64_t &n_recs, uint64_t &n_occ) {
+static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, uint64_t &n_recs, uint64_t &n_occ,
+                           size_t c0 = 0, size_t c1 = ~(size_t)0) {
     n_recs = 0;
     n_occ = 0;
+    c1 = std::min(c1, B.chunk_first.size() - 1);  // chunks [c0, c1) of the batch (default: all of it)
     if (B.n_reads == 0) {
         CK(cudaEventRecord(h->ev[1], h->stream));
         return BRISK_OK;
@@ -445,8 +449,8 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
         h->last_launches += 3;
     }
     // expected density of superkmers is 2/(w+1) per k-mer; leave slack, retry on overflow
-    uint64_t upper = B.total_bytes;  // >= number of k-mer occurrences
-    uint64_t guess = (uint64_t)(3.0 * (double)upper / (h->P.w + 1)) + B.n_reads + 4096;
+    uint64_t upper = B.chunk_byte[c1] - B.chunk_byte[c0];  // >= number of k-mer occurrences
+    uint64_t guess = (uint64_t)(3.0 * (double)upper / (h->P.w + 1)) + (B.chunk_first[c1] - B.chunk_first[c0]) + 4096;
     uint64_t cap = std::min(upper + 1, guess);
     for (int attempt = 0; attempt < 2; attempt++) {
         CK(h->d_recs.ensure(cap * RW * sizeof(uint64_t)));
@@ -460,7 +464,7 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
         out.kmer_base = with_occ ? (const u64 *)h->d_kmer_base.p : nullptr;
         // chunk by chunk: pack + enumerate of a chunk run while the next chunk's bases are still on their way; the
         // records of all chunks accumulate behind the same device counter
-        for (size_t c = 0; c + 1 < B.chunk_first.size(); c++) {
+        for (size_t c = c0; c < c1; c++) {
             int prc = pack_chunk(h, B, c);
             if (prc) return prc;
             if (c == 0) CK(cudaEventRecord(h->ev[1], h->stream));
@@ -776,11 +780,13 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     int rc = stage_reads(h, bases, offsets, n_reads, B);
     if (rc) return rc;
     const bool with_occ = slots || flags || data_out;
+    const bool sharded = h->comm && h->comm->n > 1;
+    // (A variant that also ran the store kernel chunk by chunk was measured: no gain — the e2e step is bound by the
+    // 541 MB of H2D per step at about 26 GB/s on this box — and it made the stage timings inseparable; not kept.)
     uint64_t n_recs = 0, n_occ = 0;
     rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
     if (rc) return rc;
     CK(cudaEventRecord(h->ev[2], h->stream));
-    const bool sharded = h->comm && h->comm->n > 1;
     Exchange X;
     X.recs = (const u64 *)h->d_recs.p;
     X.n = n_recs;

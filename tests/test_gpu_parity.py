@@ -274,3 +274,35 @@ def test_tagged_enumeration_is_in_reference_order(name):
         for grp in np.split(np.arange(len(e["lo"])), bounds):
             want.append(tuple(((int(e["hi"][i]) << 64) | int(e["lo"][i]), int(e["idx"][i])) for i in grp))
     assert got == want
+
+
+@pytest.mark.parametrize("kmb", [(31, 15, 12), (63, 21, 14)])
+def test_chunked_host_input_equals_device_input(kmb):
+    """Host buffers larger than 16 MB arrive in chunks that are pipelined with the kernels; the result must be the one
+    of the same reads handed over as one device-resident batch (and, on a sample, the oracle's)."""
+    import torch
+    from brisk_b200 import Brisk, Parameters, synth
+    from oracle.oracle import Oracle
+    k, m, b = kmb
+    L, n = 150, 240000  # 36 MB of bases -> 5 chunks
+    gen = synth.genome(2_000_000, 11)
+    arr = synth.reads(gen, L, 11, 0, n).reshape(-1)
+    offs = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
+    host = Brisk(Parameters(k, m, b))
+    host.count_reads(arr, offs)
+    dev = Brisk(Parameters(k, m, b))
+    dev.count_reads(torch.from_numpy(arr).cuda(), torch.from_numpy(offs.astype(np.int64)).cuda())
+    assert host.stats()["nb_kmers"] == dev.stats()["nb_kmers"]
+    assert G.dump_sha(*host.dump()) == G.dump_sha(*dev.dump())
+    assert host.query_reads(arr, offs) == dev.query_reads(arr, offs)
+    assert host.query_reads(arr, offs)[0] == n * (L - k + 1)
+    # per-occurrence outputs with chunked input (only the copy / enumerate stages are pipelined there)
+    f1, d1 = host.get_reads(arr, offs)
+    f2, d2 = dev.get_reads(torch.from_numpy(arr).cuda(), torch.from_numpy(offs.astype(np.int64)).cuda())
+    assert np.array_equal(f1, f2) and np.array_equal(d1, d2) and f1.all()
+    # oracle on the first reads: counts of their k-mers in the whole set are >= their counts in the sample
+    o = Oracle(k, m, b)
+    o.count_reads(arr[:2000 * L], offs[:2001])
+    lo, hi, ix, cnt = o.dump()
+    slots, data = host.get_kmers(Brisk.pack_kmers(lo, hi, ix))
+    assert (slots != np.uint64(0xFFFFFFFFFFFFFFFF)).all() and (data >= cnt).all()
