@@ -283,8 +283,8 @@ def run_ours(args):
                    "%.1f GB store)" % (st_dev["memory_usage"] / 1e9), "stored_kmers": st_dev["nb_kmers"]},
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / steps,
-                "h2d_bytes_per_step": 2 * (BATCH_READS * READ_LEN + 8 * (BATCH_READS + 1)),
-                "d2h_bytes_per_step": 32 + 16 + 8 + 8},
+                "h2d_bytes_per_step": world * 2 * (BATCH_READS * READ_LEN + 8 * (BATCH_READS + 1)),
+                "d2h_bytes_per_step": world * (32 + 16 + 8 + 8)},
         "gpu_launches": acc_dev["launches"],
         "stage_ms_per_step": {"pack": acc_dev["pack_ms"] / steps, "enumerate": acc_dev["enum_ms"] / steps,
                               "insert": acc_dev["store_ms"] / steps, "query_enumerate": acc_dev["q_enum_ms"] / steps,
