@@ -157,6 +157,11 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: anything a library prints to fd 1 meanwhile (NCCL announces its version
+    # there at communicator creation) is sent to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -298,7 +303,7 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": res["value"], "unit": UNIT, "cores": threads, "kind": "reference",
                                     "sample": "oracle/_ref/ref_dump steps: %d reads per step, 6 timed steps after 2 warm-up, "
                                               "same read set" % args.sample_reads}
-    print(json.dumps(line))
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -306,3 +306,43 @@ def test_chunked_host_input_equals_device_input(kmb):
     lo, hi, ix, cnt = o.dump()
     slots, data = host.get_kmers(Brisk.pack_kmers(lo, hi, ix))
     assert (slots != np.uint64(0xFFFFFFFFFFFFFFFF)).all() and (data >= cnt).all()
+
+
+@pytest.mark.parametrize("kmb,L", [((63, 21, 14), 250), ((31, 19, 16), 150), ((64, 23, 14), 250)])
+def test_full_batch_size_properties(kmb, L):
+    """BASELINE-size batches (2^20 reads per call) through size-independent properties: every inserted occurrence is
+    found again, the counts add up to the occurrences, re-inserting creates nothing, a decoy genome hits (almost)
+    nothing, and the store agrees with itself after growing."""
+    import torch
+    from brisk_b200 import Brisk, Parameters, synth
+    k, m, b = kmb
+    n = 1 << 20
+    G_ = 20_000_000
+    gen = synth.genome(G_, 21)
+    occ = n * (L - k + 1)
+    offs = torch.from_numpy(np.arange(n + 1, dtype=np.int64) * L).cuda()
+    idx = Brisk(Parameters(k, m, b))  # no capacity hint: the store has to grow on its own
+    batches = [torch.from_numpy(synth.reads(gen, L, 21, j * n, n).reshape(-1)).cuda() for j in range(2)]
+    for bt in batches:
+        idx.count_reads(bt, offs)
+    st = idx.stats()
+    lo, hi, ix, cnt = idx.dump()
+    assert len(lo) == st["nb_kmers"]
+    assert int(cnt.astype(np.int64).sum()) == 2 * occ  # coverage stays far below the uint8 wrap
+    assert len(set(zip(lo[:200000].tolist(), hi[:200000].tolist(), ix[:200000].tolist()))) == 200000
+    for bt in batches:
+        hits, total = idx.query_reads(bt, offs)
+        assert hits == occ and total >= occ
+    # idempotence of insert: nothing new, counts untouched
+    slots, newly = idx.insert_reads(batches[0][:4000 * L], offs[:4001])
+    assert not newly.any() and (slots != np.uint64(0xFFFFFFFFFFFFFFFF)).all()
+    assert idx.stats()["nb_kmers"] == st["nb_kmers"]
+    # a decoy genome shares (almost) no k-mer
+    decoy = synth.genome(2_000_000, 99)
+    q = torch.from_numpy(synth.reads(decoy, L, 99, 0, 100000).reshape(-1)).cuda()
+    hits, _ = idx.query_reads(q, offs[:100001])
+    assert hits < 10
+    # growing the store keeps every key and count
+    idx.reserve(4 * st["nb_kmers"])
+    assert G.dump_sha(*idx.dump()) == G.dump_sha(lo, hi, ix, cnt)
+    assert idx.query_reads(batches[1], offs)[0] == occ
