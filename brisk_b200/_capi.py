@@ -22,6 +22,7 @@ PROTOTYPES = {
     "brisk_get_kmers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_data_ptr": (C.c_void_p, [C.c_void_p, C.c_uint64]),
     "brisk_dump": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "brisk_dump_ordered": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "brisk_stats": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_uint64)] * 5),
     "brisk_reserve": (C.c_int, [C.c_void_p, C.c_uint64]),
     "brisk_capacity": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),

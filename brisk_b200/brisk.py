@@ -231,14 +231,16 @@ class Brisk:
         return self._lib.brisk_data_ptr(self._h, int(slot))
 
     # ---- whole index
-    def dump(self):
-        """(lo, hi, idx, data) of every stored k-mer, unordered."""
+    def dump(self, ordered=False):
+        """(lo, hi, idx, data) of every stored k-mer; ordered=True: by bucket id like DenseMenuYo::next, then by
+        (minimizer_idx, kmer_s)."""
+        fn = self._lib.brisk_dump_ordered if ordered else self._lib.brisk_dump
         n = C.c_uint64()
-        self._check(self._lib.brisk_dump(self._h, None, None, 0, C.byref(n)))
+        self._check(fn(self._h, None, None, 0, C.byref(n)))
         keys = np.zeros(n.value, KMER_DT)
         data = np.zeros((n.value, self.data_size), np.uint8)
         if n.value:
-            self._check(self._lib.brisk_dump(self._h, _ptr(keys), _ptr(data), n.value, C.byref(n)))
+            self._check(fn(self._h, _ptr(keys), _ptr(data), n.value, C.byref(n)))
         return keys["lo"].copy(), keys["hi"].copy(), keys["idx"].copy(), (data[:, 0] if self.data_size == 1 else data)
 
     def stats(self):

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/brisk_b200.h"
@@ -532,7 +533,7 @@ static cudaError_t launch_partition(brisk_handle *h, uint64_t n_recs, uint32_t n
     unsigned b1 = (unsigned)std::min<uint64_t>((n_recs + PART_THREADS - 1) / PART_THREADS, 148 * 8);
     partition_count_kernel<RW><<<b1, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_totals(h));
     partition_starts_kernel<<<1, 32, 0, h->stream>>>(part_totals(h), n_ranks, part_starts(h), part_cursors(h));
-    unsigned b2 = (unsigned)std::min<uint64_t>((n_recs + PART_TILE - 1) / PART_TILE, 148 * 4);
+    unsigned b2 = (unsigned)std::min<uint64_t>((n_recs + PART_TILE - 1) / PART_TILE, 148 * 8);
     partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_cursors(h), (u64 *)h->d_send.p,
                                                                       with_occ ? (const u64 *)h->d_rec_occ.p : nullptr,
                                                                       with_occ ? (u64 *)h->d_send_occ.p : nullptr);
@@ -1030,6 +1031,90 @@ extern "C" int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap
     CK(cudaStreamSynchronize(h->stream));
     if (got != nk) return fail(BRISK_E_CUDA, "dump found " + std::to_string(got) + " keys, expected " + std::to_string(nk));
     return BRISK_OK;
+}
+
+// ---- ordered dump: the stored set in the order DenseMenuYo::next walks it at bucket level
+// (increasing bucket id, brisk/DenseMenuYo.hpp:476-521); inside a bucket the reference's order is its arena's insertion
+// order, here (minimizer_idx, kmer_s) ascending so that the result is deterministic.
+__global__ void __launch_bounds__(256) dump_sortkeys_kernel(const BriskParams P, const KmerIn *__restrict__ keys, u64 n, u64 *lo, u64 *hi,
+                                                            u64 *top, u32 *perm) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const KmerIn k = keys[i];
+    lo[i] = k.lo;
+    hi[i] = k.hi;
+    top[i] = (bucket_of_kmer(P, k.lo, k.hi, (int)k.idx) << 8) | k.idx;
+    perm[i] = (u32)i;
+}
+__global__ void __launch_bounds__(256) gather64_kernel(const u64 *__restrict__ src, const u32 *__restrict__ perm, u64 n, u64 *dst) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[perm[i]];
+}
+__global__ void __launch_bounds__(256) gather_dump_kernel(const KmerIn *__restrict__ keys, const unsigned char *__restrict__ data,
+                                                          u32 data_size, const u32 *__restrict__ perm, u64 n, KmerIn *okeys,
+                                                          unsigned char *odata) {
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 s = perm[i];
+    if (okeys) okeys[i] = keys[s];
+    if (odata) for (u32 q = 0; q < data_size; q++) odata[i * data_size + q] = data[(u64)s * data_size + q];
+}
+
+extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    uint64_t nk = 0;
+    int rc = brisk_dump(h, nullptr, nullptr, 0, &nk);
+    if (rc) return rc;
+    if (n) *n = nk;
+    if (!keys && !data) return BRISK_OK;
+    if (cap < nk) return fail(BRISK_E_CAPACITY, "dump buffers too small");
+    if (nk >= (1ull << 32)) return fail(BRISK_E_CAPACITY, "ordered dump handles fewer than 2^32 k-mers per shard");
+    if (nk == 0) return BRISK_OK;
+    CK(cudaSetDevice(h->device));
+    DevBuf ukeys, udata, lo, hi, top, tmpk, perm, perm2, cubtmp, okeys, odata;
+    auto cleanup = [&]() { for (DevBuf *b : {&ukeys, &udata, &lo, &hi, &top, &tmpk, &perm, &perm2, &cubtmp, &okeys, &odata}) b->release(); };
+    auto body = [&]() -> int {
+        CK(ukeys.ensure(nk * sizeof(KmerIn)));
+        CK(udata.ensure(nk * h->data_size));
+        int r = brisk_dump(h, (brisk_kmer *)ukeys.p, udata.p, nk, &nk);  // unordered, device to device
+        if (r) return r;
+        std::lock_guard<std::mutex> lock(h->mu);
+        for (DevBuf *b : {&lo, &hi, &top, &tmpk}) CK(b->ensure(nk * sizeof(u64)));
+        CK(perm.ensure(nk * sizeof(u32)));
+        CK(perm2.ensure(nk * sizeof(u32)));
+        const unsigned blocks = (unsigned)((nk + 255) / 256);
+        dump_sortkeys_kernel<<<blocks, 256, 0, h->stream>>>(h->P, (const KmerIn *)ukeys.p, nk, (u64 *)lo.p, (u64 *)hi.p, (u64 *)top.p, (u32 *)perm.p);
+        CK(cudaGetLastError());
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, (u64 *)lo.p, (u64 *)tmpk.p, (u32 *)perm.p, (u32 *)perm2.p, (int)nk, 0, 64, h->stream));
+        CK(cubtmp.ensure(tb));
+        // least-significant first: kmer_s low word, high word, then (bucket id, minimizer_idx); every pass is stable
+        u32 *pa = (u32 *)perm.p, *pb = (u32 *)perm2.p;
+        CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 64, h->stream));
+        std::swap(pa, pb);
+        if (h->P.key_words == 2) {
+            gather64_kernel<<<blocks, 256, 0, h->stream>>>((const u64 *)hi.p, pa, nk, (u64 *)lo.p);
+            CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 2 * h->P.k - 64, h->stream));
+            std::swap(pa, pb);
+        }
+        gather64_kernel<<<blocks, 256, 0, h->stream>>>((const u64 *)top.p, pa, nk, (u64 *)lo.p);
+        CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 2 * h->P.b + 8, h->stream));
+        std::swap(pa, pb);
+        const bool k_dev = is_device_ptr(keys), d_dev = is_device_ptr(data);
+        KmerIn *ok = nullptr;
+        unsigned char *od = nullptr;
+        if (keys) { if (k_dev) ok = (KmerIn *)keys; else { CK(okeys.ensure(nk * sizeof(KmerIn))); ok = (KmerIn *)okeys.p; } }
+        if (data) { if (d_dev) od = (unsigned char *)data; else { CK(odata.ensure(nk * h->data_size)); od = (unsigned char *)odata.p; } }
+        gather_dump_kernel<<<blocks, 256, 0, h->stream>>>((const KmerIn *)ukeys.p, (const unsigned char *)udata.p, h->data_size, pa, nk, ok, od);
+        CK(cudaGetLastError());
+        if (keys && !k_dev) CK(cudaMemcpyAsync(keys, ok, nk * sizeof(KmerIn), cudaMemcpyDeviceToHost, h->stream));
+        if (data && !d_dev) CK(cudaMemcpyAsync(data, od, nk * h->data_size, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        return BRISK_OK;
+    };
+    rc = body();
+    cleanup();
+    return rc;
 }
 
 extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t *nb_kmers, uint64_t *device_bytes,

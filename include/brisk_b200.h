@@ -107,6 +107,11 @@ void *brisk_data_ptr(brisk_t *h, uint64_t slot);
  * minimizer_idx, DATA), unordered.  keys/data may be NULL to only count. */
 int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n);
 
+/* The same set in the order DenseMenuYo::next walks it at bucket level (brisk/DenseMenuYo.hpp:476-521): increasing
+ * bucket id; inside a bucket by (minimizer_idx, kmer_s) (the reference's inner order is its arena's insertion order).
+ * On a sharded index every rank dumps its own buckets. */
+int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n);
+
 /* Brisk::stats (brisk/Brisk.hpp:194-197, brisk/DenseMenuYo.hpp:545-568). nb_skmers = superkmer records
  * that created at least one k-mer; largest_bucket is not tracked (reported 0): both depend on
  * insertion order in the reference. */

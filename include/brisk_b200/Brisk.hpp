@@ -247,12 +247,13 @@ public:
     void protect_data(const kmer_full &kmer) { stripes_[stripe_of(kmer)].lock(); }
     void unprotect_data(const kmer_full &kmer) { stripes_[stripe_of(kmer)].unlock(); }
 
-    // brisk/Brisk.hpp:166-179: walks the stored set (a snapshot taken at restart / first call; order unspecified)
+    // brisk/Brisk.hpp:166-179: walks the stored set (a snapshot taken at restart / first call) bucket by bucket in
+    // increasing bucket id like DenseMenuYo::next (brisk/DenseMenuYo.hpp:476-521)
     void restart_kmer_enumeration() {
         uint64_t n = 0;
-        brisk_check(brisk_dump(menu, nullptr, nullptr, 0, &n));
+        brisk_check(brisk_dump_ordered(menu, nullptr, nullptr, 0, &n));
         snap_.assign(n, brisk_kmer());
-        if (n) brisk_check(brisk_dump(menu, snap_.data(), nullptr, n, &n));
+        if (n) brisk_check(brisk_dump_ordered(menu, snap_.data(), nullptr, n, &n));
         cursor_ = 0;
         have_snap_ = true;
     }

@@ -317,7 +317,7 @@ def test_full_batch_size_properties(kmb, L):
     from brisk_b200 import Brisk, Parameters, synth
     k, m, b = kmb
     n = 1 << 20
-    G_ = 20_000_000
+    G_ = 8_000_000  # 2 batches = 65x coverage: counts stay below the uint8 wrap
     gen = synth.genome(G_, 21)
     occ = n * (L - k + 1)
     offs = torch.from_numpy(np.arange(n + 1, dtype=np.int64) * L).cuda()
@@ -346,3 +346,32 @@ def test_full_batch_size_properties(kmb, L):
     idx.reserve(4 * st["nb_kmers"])
     assert G.dump_sha(*idx.dump()) == G.dump_sha(lo, hi, ix, cnt)
     assert idx.query_reads(batches[1], offs)[0] == occ
+
+
+@pytest.mark.parametrize("name", ["test_fa_k63", "debug_fa_k31", "synth_cfg3", "synth_cfg5", "test_fa_k64"])
+def test_ordered_dump_walks_buckets_in_id_order(name):
+    """brisk_dump_ordered = the set of brisk_dump, bucket ids non-decreasing (DenseMenuYo::next's outer order), (minimizer_idx, kmer_s)
+    ascending inside a bucket; bucket ids recomputed on the host from the oracle's bfc_hash."""
+    from oracle.oracle import Oracle
+    c = G.case(name)
+    idx = make_index(c)
+    bases, offs = G.flat(G.reads_of(c))
+    idx.count_reads(bases, offs)
+    lo, hi, ix, cnt = idx.dump(ordered=True)
+    assert G.dump_sha(lo, hi, ix, cnt) == c["dump_sha256"]
+    o = Oracle(c["k"], c["m"], c["b"])
+    k, m, b = c["k"], c["m"], c["b"]
+    s, m_mask = (m - b + 1) // 2, (1 << (2 * m)) - 1
+    step = max(1, len(lo) // 3000)  # the host loop is slow: check a regular sample of consecutive pairs
+    prev = None
+    for i in range(0, len(lo)):
+        if i % step > 1:
+            prev = None
+            continue
+        val = (int(hi[i]) << 64) | int(lo[i])
+        w = (val >> (2 * int(ix[i]))) & m_mask
+        bucket = ((o.bfc_hash(w) & m_mask) >> (2 * s)) & ((1 << (2 * b)) - 1)
+        key = (bucket, int(ix[i]), val)
+        if prev is not None:
+            assert prev < key
+        prev = key
