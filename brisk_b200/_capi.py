@@ -29,6 +29,10 @@ PROTOTYPES = {
     "brisk_sync": (C.c_int, [C.c_void_p]),
     "brisk_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]),
+    "brisk_parse_fasta": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                    C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "brisk_count_fasta": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "brisk_query_fasta": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "brisk_partition_reads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint64,
                                         C.c_void_p, C.POINTER(C.c_uint32)]),
     "brisk_apply_records": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

@@ -158,6 +158,37 @@ class Brisk:
         self._check(self._lib.brisk_query_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets), C.byref(hits), C.byref(total)))
         return hits.value, total.value
 
+    # ---- FASTA ingest (getLineFasta + clean_dna of apps/counter.cpp on the device)
+    @staticmethod
+    def _text(text):
+        if isinstance(text, (bytes, bytearray)):
+            text = np.frombuffer(bytes(text), np.uint8)
+        n = text.numel() if hasattr(text, "numel") else len(text)
+        return text, n
+
+    def parse_fasta(self, text):
+        """(bases, offsets) of the reads the reference's reader loop would hand to count_sequence."""
+        text, n = self._text(text)
+        nb, nr = C.c_uint64(), C.c_uint64()
+        self._check(self._lib.brisk_parse_fasta(self._h, _ptr(text) if n else None, n, None, 0, None, 0, C.byref(nb), C.byref(nr)))
+        bases = np.zeros(nb.value, np.uint8)
+        offs = np.zeros(nr.value + 1, np.uint64)
+        self._check(self._lib.brisk_parse_fasta(self._h, _ptr(text) if n else None, n, _ptr(bases), nb.value, _ptr(offs), nr.value,
+                                                C.byref(nb), C.byref(nr)))
+        return bases, offs
+
+    def count_fasta(self, text):
+        text, n = self._text(text)
+        nr = C.c_uint64()
+        self._check(self._lib.brisk_count_fasta(self._h, _ptr(text) if n else None, n, C.byref(nr)))
+        return nr.value
+
+    def query_fasta(self, text):
+        text, n = self._text(text)
+        hits, total = C.c_uint64(), C.c_uint64()
+        self._check(self._lib.brisk_query_fasta(self._h, _ptr(text) if n else None, n, C.byref(hits), C.byref(total)))
+        return hits.value, total.value
+
     # ---- the two halves of the routed path (multi-GPU building blocks)
     def partition_reads(self, bases, offsets, n_ranks):
         """(records grouped by owner rank, starts[n_ranks + 1]) — what a rank sends in the exchange."""

@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "enumerate.cuh"
 #include "partition.cuh"
+#include "fasta.cuh"
 #include "store.cuh"
 #include "comm.cuh"
 
@@ -84,12 +85,13 @@ struct brisk_handle {
     DevBuf d_bases, d_offsets, d_packed, d_recs, d_rec_occ, d_kmer_base, d_cnt, d_out_slots, d_out_flags, d_out_data,
         d_kmers, d_cub;
     // partition / exchange (sharded index and the partition entry point)
+    DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_ls, d_fa_a, d_fa_b, d_fa_kind;  // FASTA ingest
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
     double2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
     u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
     Comm *comm = nullptr;
     uint64_t *d_rec_count = nullptr;  // device counter
-    std::mutex mu;
+    std::recursive_mutex mu;  // recursive: the FASTA entry points hold it across parse + run_reads
 };
 
 static bool is_device_ptr(const void *p) {
@@ -296,7 +298,8 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaStreamSynchronize(h->stream);
     DevBuf *bufs[] = {&h->d_bases, &h->d_offsets, &h->d_packed, &h->d_recs, &h->d_rec_occ, &h->d_kmer_base, &h->d_cnt,
                       &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_send, &h->d_send_occ,
-                      &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data};
+                      &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data,
+                      &h->d_fa_text, &h->d_fa_bases, &h->d_fa_offsets, &h->d_fa_ls, &h->d_fa_a, &h->d_fa_b, &h->d_fa_kind};
     for (DevBuf *b : bufs) b->release();
     if (h->comm) {
         if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
@@ -774,7 +777,7 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
                      uint64_t *slots, uint8_t *flags, void *data_out, uint64_t *agg_out = nullptr) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     if (n_reads && (!bases || !offsets)) return fail(BRISK_E_PARAM, "null input");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     ReadBatch B;
@@ -885,7 +888,7 @@ extern "C" int brisk_get_reads(brisk_t *h, const char *bases, const uint64_t *of
 extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *recs,
                                      uint64_t cap_recs, uint64_t *n_recs_out, uint32_t *rec_words) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
@@ -914,7 +917,7 @@ extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64
 extern "C" int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *recs,
                                             uint64_t cap_recs, uint64_t *n_recs_out, uint32_t *rec_words, uint64_t *occ) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
@@ -943,7 +946,7 @@ static int run_kmers(brisk_handle *h, const brisk_kmer *kmers, uint64_t n, int m
                      void *data_out) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     if (n && !kmers) return fail(BRISK_E_PARAM, "null input");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     if (n == 0) return BRISK_OK;
@@ -1007,7 +1010,7 @@ extern "C" void *brisk_data_ptr(brisk_t *h, uint64_t slot) {
 
 extern "C" int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     if (n) *n = h->n_keys;
@@ -1078,7 +1081,7 @@ extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint
         CK(udata.ensure(nk * h->data_size));
         int r = brisk_dump(h, (brisk_kmer *)ukeys.p, udata.p, nk, &nk);  // unordered, device to device
         if (r) return r;
-        std::lock_guard<std::mutex> lock(h->mu);
+        std::lock_guard<std::recursive_mutex> lock(h->mu);
         for (DevBuf *b : {&lo, &hi, &top, &tmpk}) CK(b->ensure(nk * sizeof(u64)));
         CK(perm.ensure(nk * sizeof(u32)));
         CK(perm2.ensure(nk * sizeof(u32)));
@@ -1120,7 +1123,7 @@ extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint
 extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t *nb_kmers, uint64_t *device_bytes,
                            uint64_t *largest_bucket) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     uint64_t nb = 0;
     CK(cudaMemsetAsync(h->counters + 4, 0, sizeof(uint64_t), h->stream));
@@ -1148,7 +1151,7 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
 
 extern "C" int brisk_reserve(brisk_t *h, uint64_t n_keys) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->hint = std::max(h->hint, n_keys);
     int rc = grow_to(h, pow2ceil(std::max<uint64_t>(n_keys * 2, 1u << 16)));
@@ -1169,7 +1172,7 @@ extern "C" int brisk_sync(brisk_t *h) {
 }
 extern "C" int brisk_set_stream(brisk_t *h, void *stream) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     h->stream = stream ? (cudaStream_t)stream : h->own_stream;
@@ -1182,13 +1185,112 @@ extern "C" int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches) 
     return BRISK_OK;
 }
 
+// ---- FASTA ingest: getLineFasta + clean_dna of apps/counter.cpp:128-190 on the device
+// parses `text` into h->d_fa_bases (upper-cased ACGT runs, dense) and h->d_fa_offsets (n_reads + 1 run starts)
+static int parse_fasta(brisk_handle *h, const char *text, uint64_t n, uint64_t &n_bases, uint64_t &n_reads) {
+    n_bases = n_reads = 0;
+    if (n >= 0xfffffffeull) return fail(BRISK_E_PARAM, "FASTA text must be shorter than 2^32 - 2 bytes per call (split at a record boundary)");
+    CK(h->d_fa_offsets.ensure((n / 2 + 2) * sizeof(uint64_t)));
+    if (n == 0) {
+        CK(cudaMemsetAsync(h->d_fa_offsets.p, 0, sizeof(uint64_t), h->stream));
+        CK(h->d_fa_bases.ensure(16));
+        return BRISK_OK;
+    }
+    const unsigned char *d_text = (const unsigned char *)text;
+    if (!is_device_ptr(text)) {
+        CK(h->d_fa_text.ensure(n));
+        CK(cudaMemcpyAsync(h->d_fa_text.p, text, n, cudaMemcpyHostToDevice, h->stream));
+        d_text = (const unsigned char *)h->d_fa_text.p;
+    }
+    CK(h->d_fa_bases.ensure(n + 16));
+    CK(h->d_fa_ls.ensure(n * sizeof(u32)));
+    CK(h->d_fa_a.ensure(n * sizeof(u64)));
+    CK(h->d_fa_b.ensure(n * sizeof(u64)));
+    CK(h->d_fa_kind.ensure(n));
+    u32 *ls = (u32 *)h->d_fa_ls.p;
+    u64 *A = (u64 *)h->d_fa_a.p, *Bf = (u64 *)h->d_fa_b.p;
+    unsigned char *kind = (unsigned char *)h->d_fa_kind.p;
+    const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+    size_t t1 = 0, t2 = 0, t3 = 0;
+    CK(cub::DeviceScan::InclusiveScan(nullptr, t1, ls, ls, MaxOp32(), (int64_t)n, h->stream));
+    CK(cub::DeviceScan::ExclusiveScan(nullptr, t2, A, Bf, MaxOp64(), (u64)0, (int64_t)n, h->stream));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, t3, A, Bf, (int64_t)n, h->stream));
+    CK(h->d_cub.ensure(std::max(t1, std::max(t2, t3))));
+    fasta_linestart_kernel<<<blocks, 256, 0, h->stream>>>(d_text, n, ls);
+    CK(cub::DeviceScan::InclusiveScan(h->d_cub.p, t1, ls, ls, MaxOp32(), (int64_t)n, h->stream));
+    fasta_classify_kernel<<<blocks, 256, 0, h->stream>>>(d_text, n, ls, A, kind);
+    CK(cub::DeviceScan::ExclusiveScan(h->d_cub.p, t2, A, Bf, MaxOp64(), (u64)0, (int64_t)n, h->stream));   // Bf = nearest non-SKIP before
+    fasta_flags_kernel<<<blocks, 256, 0, h->stream>>>(kind, Bf, n, A);                                     // A = flags
+    CK(cub::DeviceScan::ExclusiveSum(h->d_cub.p, t3, A, Bf, (int64_t)n, h->stream));                        // Bf = positions
+    fasta_emit_kernel<<<blocks, 256, 0, h->stream>>>(d_text, A, Bf, n, (unsigned char *)h->d_fa_bases.p, (u64 *)h->d_fa_offsets.p);
+    CK(cudaGetLastError());
+    h->last_launches += 7;
+    uint64_t last[2];
+    CK(cudaMemcpyAsync(&last[0], A + (n - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&last[1], Bf + (n - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    const uint64_t tot = last[0] + last[1];
+    n_bases = tot & 0xffffffffull;
+    n_reads = tot >> 32;
+    CK(cudaMemcpyAsync((u64 *)h->d_fa_offsets.p + n_reads, &n_bases, sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return BRISK_OK;
+}
+
+extern "C" int brisk_parse_fasta(brisk_t *h, const char *text, uint64_t n_bytes, char *bases, uint64_t cap_bases, uint64_t *offsets,
+                                 uint64_t cap_reads, uint64_t *n_bases_out, uint64_t *n_reads_out) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    uint64_t nb = 0, nr = 0;
+    int rc = parse_fasta(h, text, n_bytes, nb, nr);
+    if (rc) return rc;
+    if (n_bases_out) *n_bases_out = nb;
+    if (n_reads_out) *n_reads_out = nr;
+    if (bases) {
+        if (cap_bases < nb) return fail(BRISK_E_CAPACITY, "bases buffer too small");
+        CK(cudaMemcpyAsync(bases, h->d_fa_bases.p, nb, is_device_ptr(bases) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (offsets) {
+        if (cap_reads < nr) return fail(BRISK_E_CAPACITY, "offsets buffer too small (needs n_reads + 1 entries)");
+        CK(cudaMemcpyAsync(offsets, h->d_fa_offsets.p, (nr + 1) * sizeof(uint64_t),
+                           is_device_ptr(offsets) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return BRISK_OK;
+}
+
+// count_fasta / query_fasta of the demo app (apps/counter.cpp:197-226, :314-345) for one text buffer
+extern "C" int brisk_count_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *n_reads_out) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    uint64_t nb = 0, nr = 0;
+    int rc = parse_fasta(h, text, n_bytes, nb, nr);
+    if (rc) return rc;
+    if (n_reads_out) *n_reads_out = nr;
+    return brisk_count_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr);
+}
+extern "C" int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *hits, uint64_t *total) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    uint64_t nb = 0, nr = 0;
+    int rc = parse_fasta(h, text, n_bytes, nb, nr);
+    if (rc) return rc;
+    return brisk_query_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr, hits, total);
+}
+
 // ---- partition and record-level entry points (what a rank does before and after the exchange)
 extern "C" int brisk_partition_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint32_t n_ranks,
                                      uint64_t *recs, uint64_t cap_recs, uint64_t *starts, uint32_t *rec_words) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     if (n_ranks == 0 || n_ranks > PART_MAX_RANKS) return fail(BRISK_E_PARAM, "n_ranks must be 1..64");
     if (!starts) return fail(BRISK_E_PARAM, "starts is null");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
@@ -1219,7 +1321,7 @@ extern "C" int brisk_apply_records(brisk_t *h, const uint64_t *recs, uint64_t n_
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     if (n_recs && !recs) return fail(BRISK_E_PARAM, "null input");
     if (op < 0 || op > 2) return fail(BRISK_E_PARAM, "op must be 0 (count), 1 (insert) or 2 (get)");
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     h->last_launches = 0;
     const int RW = h->P.rec_words;
@@ -1282,7 +1384,7 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
     if (h->comm) return fail(BRISK_E_PARAM, "the handle already has a communicator");
     if (h->n_keys) return fail(BRISK_E_PARAM, "brisk_comm_init must come before the first insertion");
     if (!g_nccl.load()) return fail(BRISK_E_COMM, g_nccl.error);
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     ncclUniqueId u;
     memcpy(&u, id, 128);

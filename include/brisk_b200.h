@@ -130,6 +130,17 @@ int brisk_set_stream(brisk_t *h, void *stream);
  * device section (ms); n_launches = kernels launched by the call. */
 int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches);
 
+/* ---- FASTA ingest on the device: what getLineFasta + clean_dna (apps/counter.cpp:128-190) hand to count_sequence
+ * with one reader thread — per record (first line of the text or any line starting with '>' = header) the maximal runs
+ * of [ACGTacgt] of its concatenated lines, upper-cased, in file order.  `text` (host or device) must hold whole
+ * records and be shorter than 2^32 - 2 bytes; split big files at a record boundary.
+ * brisk_parse_fasta: the reads as a flat buffer + n_reads + 1 offsets (outputs nullable to only count);
+ * brisk_count_fasta / brisk_query_fasta: count_fasta (apps/counter.cpp:197-226) / query_fasta (:314-345). */
+int brisk_parse_fasta(brisk_t *h, const char *text, uint64_t n_bytes, char *bases, uint64_t cap_bases, uint64_t *offsets,
+                      uint64_t cap_reads, uint64_t *n_bases, uint64_t *n_reads);
+int brisk_count_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *n_reads);
+int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *hits, uint64_t *total);
+
 /* ---- the two halves of the routed path, usable on their own.
  * brisk_partition_reads: enumerate + radix partition of the superkmer records by owner rank, as a rank does
  * before the exchange (replaces the lock-stripe routing of DenseMenuYo::insert_kmer_vector,

@@ -1,0 +1,65 @@
+"""GPU FASTA ingest (brisk_parse_fasta / brisk_count_fasta / brisk_query_fasta) against the oracle restatement of the
+reference's reader (oracle/fasta_oracle.py, pinned to the reference app by tests/test_fasta_oracle.py) and against
+the counts the unmodified reference app reported (tests/golden/fasta_golden.json)."""
+import numpy as np
+import pytest
+
+from test_fasta_oracle import GOLD, text_of
+
+pytestmark = pytest.mark.gpu
+
+
+def make(k, m, b):
+    from brisk_b200 import Brisk, Parameters
+    return Brisk(Parameters(k, m, b))
+
+
+@pytest.mark.parametrize("name", sorted({c["file"] for c in GOLD}))
+def test_parse_equals_oracle(name):
+    from oracle.fasta_oracle import fasta_reads, flat
+    data = text_of(name)
+    idx = make(31, 15, 6)
+    bases, offs = idx.parse_fasta(data)
+    wb, wo = flat(fasta_reads(data))
+    assert np.array_equal(offs, wo) and np.array_equal(bases, wb)
+
+
+def test_parse_fuzz_and_edges():
+    from oracle.fasta_oracle import fasta_reads, flat
+    idx = make(31, 15, 6)
+    rng = np.random.default_rng(8)
+    alphabet = list(b"ACGTacgtNn>\n\n\r -X")
+    texts = [b"", b"\n", b">", b">h", b"ACGT", b">h\nACGT", b">h\nACGT\n", b"\n\nACGT\n>x\n\nA\nC\n", b">a\n>b\n>c\n"]
+    texts += [bytes(rng.choice(alphabet, int(rng.integers(1, 400))).astype(np.uint8)) for _ in range(150)]
+    # one long text spanning many CTAs
+    big = bytearray()
+    for r in range(3000):
+        big += b">r%d\n" % r
+        seq = bytearray(rng.choice(list(b"ACGTacgtN"), int(rng.integers(0, 500)), p=[.2, .2, .2, .2, .04, .04, .04, .04, .04]).astype(np.uint8))
+        w = int(rng.integers(20, 120))
+        big += b"\n".join(bytes(seq[i:i + w]) for i in range(0, len(seq), w)) + b"\n"
+    texts.append(bytes(big))
+    for t in texts:
+        bases, offs = idx.parse_fasta(t)
+        wb, wo = flat(fasta_reads(t))
+        assert np.array_equal(offs, wo) and np.array_equal(bases, wb), t[:80]
+
+
+@pytest.mark.parametrize("c", GOLD, ids=lambda c: "%s-k%d" % (c["file"], c["k"]))
+def test_count_fasta_matches_reference_app(c):
+    from oracle.fasta_oracle import fasta_reads
+    data = text_of(c["file"])
+    idx = make(c["k"], c["m"], c["b"])
+    n_reads = idx.count_fasta(data)
+    reads = fasta_reads(data)
+    assert n_reads == len(reads)
+    st = idx.stats()
+    assert st["nb_kmers"] == c["nb_kmers"] and st["nb_buckets"] == c["nb_buckets"]
+    occ = sum(max(0, len(r) - c["k"] + 1) for r in reads)
+    hits, total = idx.query_fasta(data)
+    assert hits == occ and total >= occ
+    # device-resident text gives the same
+    import torch
+    idx2 = make(c["k"], c["m"], c["b"])
+    idx2.count_fasta(torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda())
+    assert idx2.stats()["nb_kmers"] == c["nb_kmers"]
