@@ -85,7 +85,7 @@ struct brisk_handle {
     DevBuf d_bases, d_offsets, d_packed, d_recs, d_rec_occ, d_kmer_base, d_cnt, d_out_slots, d_out_flags, d_out_data,
         d_kmers, d_cub;
     // partition / exchange (sharded index and the partition entry point)
-    DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_ls, d_fa_a, d_fa_b, d_fa_kind;  // FASTA ingest
+    DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_a, d_fa_b, d_fa_chunks;  // FASTA ingest
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
     double2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
     u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
@@ -299,7 +299,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     DevBuf *bufs[] = {&h->d_bases, &h->d_offsets, &h->d_packed, &h->d_recs, &h->d_rec_occ, &h->d_kmer_base, &h->d_cnt,
                       &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_send, &h->d_send_occ,
                       &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data,
-                      &h->d_fa_text, &h->d_fa_bases, &h->d_fa_offsets, &h->d_fa_ls, &h->d_fa_a, &h->d_fa_b, &h->d_fa_kind};
+                      &h->d_fa_text, &h->d_fa_bases, &h->d_fa_offsets, &h->d_fa_a, &h->d_fa_b, &h->d_fa_chunks};
     for (DevBuf *b : bufs) b->release();
     if (h->comm) {
         if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
@@ -1203,37 +1203,23 @@ static int parse_fasta(brisk_handle *h, const char *text, uint64_t n, uint64_t &
         d_text = (const unsigned char *)h->d_fa_text.p;
     }
     CK(h->d_fa_bases.ensure(n + 16));
-    CK(h->d_fa_ls.ensure(n * sizeof(u32)));
-    CK(h->d_fa_a.ensure(n * sizeof(u64)));
-    CK(h->d_fa_b.ensure(n * sizeof(u64)));
-    CK(h->d_fa_kind.ensure(n));
-    u32 *ls = (u32 *)h->d_fa_ls.p;
-    u64 *A = (u64 *)h->d_fa_a.p, *Bf = (u64 *)h->d_fa_b.p;
-    unsigned char *kind = (unsigned char *)h->d_fa_kind.p;
-    const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 16);
-    size_t t1 = 0, t2 = 0, t3 = 0;
-    CK(cub::DeviceScan::InclusiveScan(nullptr, t1, ls, ls, MaxOp32(), (int64_t)n, h->stream));
-    CK(cub::DeviceScan::ExclusiveScan(nullptr, t2, A, Bf, MaxOp64(), (u64)0, (int64_t)n, h->stream));
-    CK(cub::DeviceScan::ExclusiveSum(nullptr, t3, A, Bf, (int64_t)n, h->stream));
-    CK(h->d_cub.ensure(std::max(t1, std::max(t2, t3))));
-    fasta_linestart_kernel<<<blocks, 256, 0, h->stream>>>(d_text, n, ls);
-    CK(cub::DeviceScan::InclusiveScan(h->d_cub.p, t1, ls, ls, MaxOp32(), (int64_t)n, h->stream));
-    fasta_classify_kernel<<<blocks, 256, 0, h->stream>>>(d_text, n, ls, A, kind);
-    CK(cub::DeviceScan::ExclusiveScan(h->d_cub.p, t2, A, Bf, MaxOp64(), (u64)0, (int64_t)n, h->stream));   // Bf = nearest non-SKIP before
-    fasta_flags_kernel<<<blocks, 256, 0, h->stream>>>(kind, Bf, n, A);                                     // A = flags
-    CK(cub::DeviceScan::ExclusiveSum(h->d_cub.p, t3, A, Bf, (int64_t)n, h->stream));                        // Bf = positions
-    fasta_emit_kernel<<<blocks, 256, 0, h->stream>>>(d_text, A, Bf, n, (unsigned char *)h->d_fa_bases.p, (u64 *)h->d_fa_offsets.p);
+    const uint64_t n_tiles = (n + FA_TILE - 1) / FA_TILE;
+    CK(h->d_fa_a.ensure(n_tiles * sizeof(FaSummary)));
+    CK(h->d_fa_b.ensure(n_tiles * sizeof(FaTileEntry)));
+    u64 *totals = part_matrix(h);  // two scratch words
+    CK(h->d_fa_chunks.ensure(n_tiles * FA_THREADS * sizeof(uint4)));
+    fasta_summarize_kernel<<<(unsigned)n_tiles, FA_THREADS, 0, h->stream>>>(d_text, n, (FaSummary *)h->d_fa_a.p, (uint4 *)h->d_fa_chunks.p);
+    fasta_tiles_kernel<<<1, 1024, 0, h->stream>>>((const FaSummary *)h->d_fa_a.p, (u32)n_tiles, (FaTileEntry *)h->d_fa_b.p, totals,
+                                                  (u64 *)h->d_fa_offsets.p);
+    fasta_emit_kernel<<<(unsigned)n_tiles, FA_THREADS, 0, h->stream>>>(d_text, n, (const FaTileEntry *)h->d_fa_b.p, (const uint4 *)h->d_fa_chunks.p,
+                                                                       (unsigned char *)h->d_fa_bases.p, (u64 *)h->d_fa_offsets.p);
     CK(cudaGetLastError());
-    h->last_launches += 7;
-    uint64_t last[2];
-    CK(cudaMemcpyAsync(&last[0], A + (n - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(&last[1], Bf + (n - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    h->last_launches += 3;
+    uint64_t tot[2];
+    CK(cudaMemcpyAsync(tot, totals, sizeof(tot), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    const uint64_t tot = last[0] + last[1];
-    n_bases = tot & 0xffffffffull;
-    n_reads = tot >> 32;
-    CK(cudaMemcpyAsync((u64 *)h->d_fa_offsets.p + n_reads, &n_bases, sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    n_bases = tot[0];
+    n_reads = tot[1];
     return BRISK_OK;
 }
 
