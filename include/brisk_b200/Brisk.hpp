@@ -292,6 +292,16 @@ public:
     void get_kmers(const brisk_kmer *kmers, uint64_t n, uint64_t *slots, DATA *data_out) {
         brisk_check(brisk_get_kmers(menu, kmers, n, slots, data_out));
     }
+    // FASTA text (whole records, plain text) parsed on the GPU like getLineFasta + clean_dna (apps/counter.cpp:128-190);
+    // returns the number of reads found
+    uint64_t count_fasta(const char *text, uint64_t n_bytes) {
+        uint64_t n_reads = 0;
+        brisk_check(brisk_count_fasta(menu, text, n_bytes, &n_reads));
+        return n_reads;
+    }
+    void query_fasta(const char *text, uint64_t n_bytes, uint64_t &hits, uint64_t &total) {
+        brisk_check(brisk_query_fasta(menu, text, n_bytes, &hits, &total));
+    }
     // whole-read conveniences of the reference's header (brisk/Brisk.hpp:27-28)
     void count_sequence(const std::string &seq) {
         uint64_t offs[2] = {0, (uint64_t)seq.size()};
