@@ -93,6 +93,37 @@ int main(int argc, char **argv) {
         uint64_t h2 = 0, t2 = 0;
         batched.query_reads(flat.data(), offs.data(), reads.size(), h2, t2);
         printf("QUERY BATCHED hits %llu total %llu\n", (unsigned long long)h2, (unsigned long long)t2);
+        // Brisk<DATA> with a wider DATA (a parallel arena instead of the byte inside the slot): the same legacy loop with
+        // uint32_t counts, no capacity hint, so the store grows (and moves its DATA) several times on the way
+        {
+            Brisk<uint32_t> wide(params);
+            uint64_t occurrences = 0;
+            for (string &r : reads) {
+                if (r.size() < params.k) continue;
+                SuperKmerEnumerator e(r, params.k, params.m, params.dede);
+                vector<kmer_full> sk;
+                vector<bool> fresh;
+                e.next(sk);
+                while (sk.size() > 0) {
+                    fresh.clear();
+                    vector<uint32_t *> v = wide.insert_superkmer(sk, fresh);
+                    for (size_t i = 0; i < v.size(); i++) { if (fresh[i]) *v[i] = 1000000; else (*v[i])++; occurrences++; }
+                    sk.clear();
+                    e.next(sk);
+                }
+            }
+            kmer_full km;
+            uint64_t n = 0, sum = 0, bad = 0;
+            wide.restart_kmer_enumeration();
+            while (wide.next(km)) {
+                uint32_t *p = wide.get(km);
+                if (p == NULL || *p < 1000000) bad++;
+                else sum += *p - 999999;
+                n++;
+            }
+            printf("WIDE kmers %llu sum %llu occurrences %llu bad %llu\n", (unsigned long long)n, (unsigned long long)sum,
+                   (unsigned long long)occurrences, (unsigned long long)bad);
+        }
         // absent key -> NULL (brisk/DenseMenuYo.hpp:331-333)
         kmer_full absent((kint)0x123456789abcdefull, 3, params.m, params.dede);
         printf("ABSENT %s\n", legacy.get(absent) == NULL ? "null" : "found");

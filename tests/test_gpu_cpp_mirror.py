@@ -48,3 +48,4 @@ def test_cpp_mirror_reproduces_reference_dump(binary, name, tmp_path):
     ql = [ln for ln in res.stdout.splitlines() if ln.startswith("QUERY ")]
     assert ql[0].split()[2:] == ql[1].split()[2:]
     assert "ABSENT null" in res.stdout
+    assert "WIDE kmers %d sum %d occurrences %d bad 0" % (c["nb_kmers"], c["occurrences"], c["occurrences"]) in res.stdout
