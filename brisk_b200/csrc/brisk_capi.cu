@@ -63,6 +63,7 @@ struct brisk_handle {
     uint32_t data_size = 1;
     uint64_t hint = 0;
     bool use_ring = true;
+    bool region_sort = true;
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[6] = {};
@@ -88,6 +89,7 @@ struct brisk_handle {
     DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_a, d_fa_b, d_fa_chunks;  // FASTA ingest
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
     double2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
+    u64 *d_part2 = nullptr;  // [64] totals, [65] starts, [64] cursors of the table-region partition
     u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
     Comm *comm = nullptr;
     uint64_t *d_rec_count = nullptr;  // device counter
@@ -248,6 +250,7 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     h->hint = capacity_hint;
     h->use_ring = k <= 32;
     if (const char *e = getenv("BRISK_ENUM_RING")) h->use_ring = atoi(e) != 0;  // development switch
+    if (const char *e = getenv("BRISK_REGION_SORT")) h->region_sort = atoi(e) != 0;  // development switch
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
@@ -275,6 +278,7 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
         h->P.dec_tab = h->dec_tab;
         h->P.dec_groups = groups;
     }
+    CK(cudaMalloc((void **)&h->d_part2, (64 + 65 + 64 + 7) * sizeof(uint64_t)));
     CK(cudaMalloc((void **)&h->d_part, (64 + 65 + 64 + 64 * 64 + 7) * sizeof(uint64_t)));
     if (flags & BRISK_F_MANAGED) CK(cudaMallocManaged((void **)&h->special, 64 * sizeof(uint32_t)));
     else CK(cudaMalloc((void **)&h->special, 64 * sizeof(uint32_t)));
@@ -306,6 +310,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
         delete h->comm;
     }
     cudaFree(h->d_part);
+    cudaFree(h->d_part2);
     cudaFree(h->dec_tab);
     cudaFree(h->slots);
     cudaFree(h->data);
@@ -491,7 +496,7 @@ template <int RW, int KW, int MODE>
 static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n_recs, OccOut O) {
     if (n_recs == 0) return cudaSuccess;
     uint64_t want = (n_recs + 255) / 256;  // one warp per 32 records
-    unsigned blocks = (unsigned)std::min<uint64_t>(want, 148 * 8 * 4);
+    unsigned blocks = (unsigned)std::min<uint64_t>(want, 148 * 4);  // persistent: 4 CTAs of 256 threads are resident per SM
     records_kernel<RW, KW, MODE><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, view_of(h), O);
     return cudaGetLastError();
 }
@@ -530,36 +535,45 @@ static u64 *part_cursors(brisk_handle *h) { return h->d_part + 64 + 65; }
 static u64 *part_matrix(brisk_handle *h) { return h->d_part + 64 + 65 + 64; }
 
 template <int RW>
-static cudaError_t launch_partition(brisk_handle *h, uint64_t n_recs, uint32_t n_ranks, bool with_occ) {
+static cudaError_t launch_partition(brisk_handle *h, u64 *scratch, const u64 *recs, const u64 *occ, uint64_t n_recs, uint32_t n_dest, int mode,
+                                    u64 *dst, u64 *dst_occ) {
     const int shift = 64 - 2 * h->P.b;
-    const u64 *recs = (const u64 *)h->d_recs.p;
+    u64 *totals = scratch, *starts = scratch + 64, *cursors = scratch + 64 + 65;
     unsigned b1 = (unsigned)std::min<uint64_t>((n_recs + PART_THREADS - 1) / PART_THREADS, 148 * 8);
-    partition_count_kernel<RW><<<b1, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_totals(h));
-    partition_starts_kernel<<<1, 32, 0, h->stream>>>(part_totals(h), n_ranks, part_starts(h), part_cursors(h));
+    partition_count_kernel<RW><<<b1, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_dest, mode, totals);
+    partition_starts_kernel<<<1, 32, 0, h->stream>>>(totals, n_dest, starts, cursors);
     unsigned b2 = (unsigned)std::min<uint64_t>((n_recs + PART_TILE - 1) / PART_TILE, 148 * 8);
-    partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_ranks, part_cursors(h), (u64 *)h->d_send.p,
-                                                                      with_occ ? (const u64 *)h->d_rec_occ.p : nullptr,
-                                                                      with_occ ? (u64 *)h->d_send_occ.p : nullptr);
+    partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_dest, mode, cursors, dst, occ, occ ? dst_occ : nullptr);
     return cudaGetLastError();
 }
 
-// d_recs (+ d_rec_occ) -> d_send (+ d_send_occ), one contiguous region per destination rank; the per-destination
-// totals and region starts stay on the device (part_totals / part_starts)
-static int partition_batch(brisk_handle *h, uint64_t n_recs, uint32_t n_ranks, bool with_occ) {
+// Radix partition of n_recs records (and, when occ is given, their occurrence tags) into one contiguous region per
+// destination.  mode 0: destination = owner rank (sharded index, before the exchange); mode 1: destination = table
+// region (STORE_REGIONS), right before the store kernel.  The per-destination totals and region starts stay on the
+// device (part_totals / part_starts).
+static int partition_records(brisk_handle *h, const u64 *recs, const u64 *occ, uint64_t n_recs, uint32_t n_dest, int mode, DevBuf &dst,
+                             DevBuf &dst_occ) {
     const int RW = h->P.rec_words;
-    CK(cudaMemsetAsync(part_totals(h), 0, 64 * sizeof(uint64_t), h->stream));
-    CK(h->d_send.ensure((n_recs + 1) * RW * sizeof(uint64_t)));
-    if (with_occ) CK(h->d_send_occ.ensure((n_recs + 1) * sizeof(uint64_t)));
+    u64 *scratch = mode == 0 ? h->d_part : h->d_part2;  // the rank partition's starts are still needed on the way back
+    CK(cudaMemsetAsync(scratch, 0, 64 * sizeof(uint64_t), h->stream));
+    CK(dst.ensure((n_recs + 1) * RW * sizeof(uint64_t)));
+    if (occ) CK(dst_occ.ensure((n_recs + 1) * sizeof(uint64_t)));
     if (n_recs == 0) {
-        partition_starts_kernel<<<1, 32, 0, h->stream>>>(part_totals(h), n_ranks, part_starts(h), part_cursors(h));
+        partition_starts_kernel<<<1, 32, 0, h->stream>>>(scratch, n_dest, scratch + 64, scratch + 64 + 65);
         CK(cudaGetLastError());
         h->last_launches += 1;
         return BRISK_OK;
     }
-    CK(RW == 2 ? launch_partition<2>(h, n_recs, n_ranks, with_occ)
-               : RW == 4 ? launch_partition<4>(h, n_recs, n_ranks, with_occ) : launch_partition<6>(h, n_recs, n_ranks, with_occ));
+    u64 *d = (u64 *)dst.p, *d_o = occ ? (u64 *)dst_occ.p : nullptr;
+    CK(RW == 2 ? launch_partition<2>(h, scratch, recs, occ, n_recs, n_dest, mode, d, d_o)
+               : RW == 4 ? launch_partition<4>(h, scratch, recs, occ, n_recs, n_dest, mode, d, d_o) : launch_partition<6>(h, scratch, recs, occ, n_recs, n_dest, mode, d, d_o));
     h->last_launches += 3;
     return BRISK_OK;
+}
+// before the exchange: d_recs (+ d_rec_occ) -> d_send (+ d_send_occ), one region per destination rank
+static int partition_batch(brisk_handle *h, uint64_t n_recs, uint32_t n_ranks, bool with_occ) {
+    return partition_records(h, (const u64 *)h->d_recs.p, with_occ ? (const u64 *)h->d_rec_occ.p : nullptr, n_recs, n_ranks, 0, h->d_send,
+                             h->d_send_occ);
 }
 
 // number of k-mers of every record -> exclusive prefix (n_recs + 1 entries) in `off`
@@ -798,6 +812,16 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         rc = exchange_records(h, n_recs, with_occ, X);
         if (rc) return rc;
     }
+    // Records in table-region order: the store kernel then walks the table region by region (L2 keeps the slots a
+    // batch revisits, the TLB sees one region at a time).  Occurrence tags travel with their records.
+    const u64 *tags = !with_occ ? nullptr : sharded ? (const u64 *)h->d_recv_occ.p : (const u64 *)h->d_rec_occ.p;
+    if (h->region_sort && X.n >= 4096) {
+        DevBuf &dst = sharded ? h->d_recs : h->d_send, &dst_occ = sharded ? h->d_rec_occ : h->d_send_occ;
+        rc = partition_records(h, X.recs, tags, X.n, STORE_REGIONS, 1, dst, dst_occ);
+        if (rc) return rc;
+        X.recs = (const u64 *)dst.p;
+        if (tags) tags = (const u64 *)dst_occ.p;
+    }
     CK(cudaEventRecord(h->ev[3], h->stream));
     if (mode != MODE_GET) {
         rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes);
@@ -827,12 +851,12 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     }
     DevBuf back_slots, back_flags, back_data;
     if (!sharded) {
-        O.rec_occ = with_occ ? (const u64 *)h->d_rec_occ.p : nullptr;
+        O.rec_occ = tags;
         O.slots = o_slots; O.flags = o_flags; O.data = o_data;
     } else if (with_occ) {
         // the owner writes its answers in arrival order; they travel back and are put in read order below
         const uint64_t n_ret = X.recv_occ_start[h->comm->n];
-        O.rec_occ = (const u64 *)h->d_recv_occ.p;
+        O.rec_occ = tags;
         if (slots) { CK(h->d_ret_slots.ensure((n_ret + 1) * sizeof(uint64_t))); O.slots = (u64 *)h->d_ret_slots.p; }
         if (flags) { CK(h->d_ret_flags.ensure(n_ret + 1)); O.flags = (unsigned char *)h->d_ret_flags.p; }
         if (data_out) { CK(h->d_ret_data.ensure((n_ret + 1) * h->data_size)); O.data = (unsigned char *)h->d_ret_data.p; }

@@ -235,7 +235,7 @@ __host__ __device__ __forceinline__ u64 slot_hash(u64 lo, u64 hi, u32 idx) {
 // ---- placement in the bucket store -----------------------------------------------------------------
 // All k-mers of a superkmer share the m-mer found at minimizer_idx (the minimizer, as it is written in the
 // superkmer's orientation) and have consecutive minimizer_idx.  The home slot of (kmer_s, idx) is therefore
-//     group_base(minimizer m-mer) + idx
+//     group_home(minimizer m-mer, its bucket id) + idx
 // so that the n k-mers of a superkmer sit in n CONSECUTIVE slots: the lanes of a warp that walk a superkmer
 // touch whole 128-byte lines instead of n random 32-byte sectors.  Collisions jump by STORE_STRIDE (>= the
 // largest superkmer), which keeps a displaced piece of a superkmer contiguous; after STORE_GROUP_PROBES jumps
@@ -254,6 +254,22 @@ __host__ __device__ __forceinline__ u64 group_base(u64 W) {
     x *= 0xD6E8FEB86659FD93ull;
     x ^= x >> 29;
     return x;
+}
+// Table regions.  The table is cut into STORE_REGIONS equal regions and a minimizer's group lives in the region chosen
+// by a hash of its BUCKET id (the record header carries the bucket id), so a batch whose records have been partitioned
+// by region (partition.cuh, mode 1) walks the table region by region: the slots a batch touches in one region (a few
+// tens of MB) stay in the 126 MB L2 while the batch's repeated k-mers come back to them, and the TLB sees one region at
+// a time.  The region hash is independent of the rank split of the sharded index.
+#define STORE_REGIONS 64u
+__host__ __device__ __forceinline__ u32 region_of_bucket(u64 bucket_id) {
+    u64 x = (bucket_id + 0x51ED270B27B4F3CFull) * 0xD6E8FEB86659FD93ull;
+    x ^= x >> 29;
+    return (u32)(x >> 40) & (STORE_REGIONS - 1);
+}
+// first slot of the group of minimizer m-mer W of bucket `bucket` in a table of mask + 1 slots (mask + 1 >= 1024)
+__host__ __device__ __forceinline__ u64 group_home(u64 W, u64 bucket, u64 mask) {
+    const u64 region_slots = (mask + 1) / STORE_REGIONS;
+    return (u64)region_of_bucket(bucket) * region_slots + (group_base(W) & (region_slots - 1));
 }
 // slot visited by probe number i (i = 0 is the home slot)
 __host__ __device__ __forceinline__ u64 probe_slot(u64 home, u64 lo, u64 hi, u32 idx, u32 i, u64 mask) {

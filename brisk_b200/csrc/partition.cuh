@@ -35,15 +35,21 @@ __host__ __device__ __forceinline__ u32 owner_of_bucket(u64 bucket_id, u32 n_ran
 #endif
 }
 
+// destination of a record: mode 0 = owner rank of its bucket (sharded index), mode 1 = table region of its bucket
+// (n_ranks = STORE_REGIONS; common.cuh)
+__device__ __forceinline__ u32 partition_dest(u64 bucket, u32 n_ranks, int mode) {
+    return mode == 0 ? owner_of_bucket(bucket, n_ranks) : region_of_bucket(bucket);
+}
+
 template <int RW>
 __global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const u64 *__restrict__ recs, u64 n_recs, int bucket_shift,
-                                                                       u32 n_ranks, u64 *__restrict__ totals) {
+                                                                       u32 n_ranks, int mode, u64 *__restrict__ totals) {
     __shared__ u32 hist[PART_MAX_RANKS];
     if (threadIdx.x < PART_MAX_RANKS) hist[threadIdx.x] = 0;
     __syncthreads();
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_recs; i += (u64)gridDim.x * blockDim.x) {
         u64 top = __ldg(recs + i * RW + (RW - 1));
-        atomicAdd(&hist[owner_of_bucket(top >> bucket_shift, n_ranks)], 1u);
+        atomicAdd(&hist[partition_dest(top >> bucket_shift, n_ranks, mode)], 1u);
     }
     __syncthreads();
     if (threadIdx.x < n_ranks && hist[threadIdx.x]) atomicAdd(totals + threadIdx.x, (u64)hist[threadIdx.x]);
@@ -65,7 +71,7 @@ __global__ void partition_starts_kernel(const u64 *totals, u32 n_ranks, u64 *sta
 // rec_occ_in / rec_occ_out (optional): the per-record read-order occurrence tag travels with its record
 template <int RW>
 __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const u64 *__restrict__ recs, u64 n_recs, int bucket_shift,
-                                                                         u32 n_ranks, u64 *__restrict__ cursors,
+                                                                         u32 n_ranks, int mode, u64 *__restrict__ cursors,
                                                                          u64 *__restrict__ out, const u64 *__restrict__ occ_in,
                                                                          u64 *__restrict__ occ_out) {
     __shared__ u32 hist[PART_MAX_RANKS];       // records of the tile per destination
@@ -96,7 +102,7 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const u
                     rec[q][i + 1] = v.y;
                 }
                 occ[q] = occ_in ? __ldcs(occ_in + base + e) : 0ull;
-                dest[q] = owner_of_bucket(rec[q][RW - 1] >> bucket_shift, n_ranks);
+                dest[q] = partition_dest(rec[q][RW - 1] >> bucket_shift, n_ranks, mode);
                 rank[q] = atomicAdd(&hist[dest[q]], 1u);
             }
         }

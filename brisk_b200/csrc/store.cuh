@@ -232,8 +232,14 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
             }
             rec_unpack_header(P, w[RW - 1], bucket, n, idx0);
             w[RW - 1] &= top_mask;
+            // every k-mer of an inserted record ends up stored, so its bucket is in use: one bit per record (checked
+            // before the atomic), not one atomic per new k-mer
+            if (MODE != MODE_GET && T.bucket_bits) {
+                const u32 bit = 1u << (bucket & 31);
+                if (!(__ldg(T.bucket_bits + (bucket >> 5)) & bit)) atomicOr(T.bucket_bits + (bucket >> 5), bit);
+            }
             // the minimizer m-mer of the record (nucleotides [idx0, idx0+m) of its first k-mer) places the whole superkmer
-            gbase = group_base(mw_extract64<RW, 3>(w, 2 * (n - 1 + idx0)) & P.m_mask);
+            gbase = group_home(mw_extract64<RW, 3>(w, 2 * (n - 1 + idx0)) & P.m_mask, bucket, T.mask);
             if (O.rec_occ) occ = O.rec_occ[ri];
         } else {
 #pragma unroll
@@ -257,11 +263,10 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                 if (src + step <= 32 && probe <= o) src += step;
             }
             const int src_l = src & 31;
-            const int s_incl = __shfl_sync(0xffffffffu, incl, src_l);
-            const int s_n = __shfl_sync(0xffffffffu, n, src_l);
-            const int s_idx0 = __shfl_sync(0xffffffffu, idx0, src_l);
-            const u64 s_bucket = __shfl_sync(0xffffffffu, bucket, src_l);
-            const u64 s_occ = __shfl_sync(0xffffffffu, occ, src_l);
+            // incl (<= 32 * 64), n (<= 64) and idx0 (< 64) of the source record in one shuffle
+            const u32 s_pack = __shfl_sync(0xffffffffu, (u32)incl | ((u32)n << 12) | ((u32)idx0 << 20), src_l);
+            const int s_incl = (int)(s_pack & 0xfffu), s_n = (int)((s_pack >> 12) & 0xffu), s_idx0 = (int)(s_pack >> 20);
+            const u64 s_occ = O.rec_occ ? __shfl_sync(0xffffffffu, occ, src_l) : 0ull;
             const u64 s_gbase = __shfl_sync(0xffffffffu, gbase, src_l);
             u64 pw[RW];
 #pragma unroll
@@ -293,7 +298,6 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
                     if (res == 1) {
                         new_keys++;
                         if (j == 0) new_recs++;
-                        store_note_new(T, s_bucket);
                     } else if (res < 0) {
                         store_park(T, lo, hi, idx, add);
                     }
@@ -338,7 +342,7 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
         {
             u64 lo = kmers[i].lo & P.kmask_lo, hi = kmers[i].hi & P.kmask_hi;
             u32 idx = kmers[i].idx;
-            const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & T.mask;
+            const u64 home = (group_home(minimizer_word(P, lo, hi, (int)idx), bucket_of_kmer(P, lo, hi, (int)idx), T.mask) + idx) & T.mask;
             u64 slot = ~0ull;
             if (MODE == MODE_GET) {
                 u32 mt = 0;
@@ -376,7 +380,7 @@ __global__ void __launch_bounds__(256) replay_kernel(const BriskParams P, const 
         u64 lo = parked[3 * i], hi = parked[3 * i + 1], x = parked[3 * i + 2];
         u32 idx = (u32)(x & 0xFF), add = (u32)(x >> 8);
         u64 slot;
-        const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & T.mask;
+        const u64 home = (group_home(minimizer_word(P, lo, hi, (int)idx), bucket_of_kmer(P, lo, hi, (int)idx), T.mask) + idx) & T.mask;
         int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
         if (res == 1) {
             atomicAdd(T.counters + 0, 1ull);
@@ -399,7 +403,7 @@ __global__ void __launch_bounds__(256) rehash_kernel(const BriskParams P, StoreV
         u64 hi = KW == 2 ? reinterpret_cast<const u64 *>(&v)[1] : 0;
         if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) continue;
         u32 idx = (v.meta & META_TAG_MASK) - 1;
-        const u64 home = (group_base(minimizer_word(P, lo, hi, (int)idx)) + idx) & to.mask;
+        const u64 home = (group_home(minimizer_word(P, lo, hi, (int)idx), bucket_of_kmer(P, lo, hi, (int)idx), to.mask) + idx) & to.mask;
         u64 s = home;
         for (u32 probes = 0;;) {
             S *p = dst + s;
