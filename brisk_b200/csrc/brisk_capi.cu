@@ -496,7 +496,15 @@ template <int RW, int KW, int MODE>
 static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n_recs, OccOut O) {
     if (n_recs == 0) return cudaSuccess;
     uint64_t want = (n_recs + 255) / 256;  // one warp per 32 records
-    unsigned blocks = (unsigned)std::min<uint64_t>(want, 148 * 4);  // persistent: 4 CTAs of 256 threads are resident per SM
+    // persistent grid: exactly the CTAs that are resident at once (B200: 148 SMs), every warp strides over the records
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, records_kernel<RW, KW, MODE>, 256, 0) != cudaSuccess || v < 1) v = 4;
+        if (const char *e = getenv("BRISK_STORE_CTAS")) v = std::max(1, atoi(e));
+        per_sm = v;
+    }
+    unsigned blocks = (unsigned)std::min<uint64_t>(want, (uint64_t)148 * per_sm);
     records_kernel<RW, KW, MODE><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, view_of(h), O);
     return cudaGetLastError();
 }

@@ -48,6 +48,10 @@ __device__ __forceinline__ u32 ld_relaxed32(const u32 *addr) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
     return v;
 }
+// the whole 32-byte slot in one request (sm_100: LDG.256): key words + meta word
+__device__ __forceinline__ void ld_relaxed256(const void *addr, u64 &a, u64 &b, u64 &c, u64 &d) {
+    asm volatile("ld.relaxed.gpu.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(addr) : "memory");
+}
 __device__ __forceinline__ void cas128(void *addr, u64 clo, u64 chi, u64 slo, u64 shi, u64 &olo, u64 &ohi) {
     asm volatile("{\n .reg .b128 c, s, d;\n mov.b128 c, {%3,%4};\n mov.b128 s, {%5,%6};\n"
                  " atom.global.relaxed.gpu.cas.b128 d, [%2], c, s;\n mov.b128 {%0,%1}, d;\n}\n"
@@ -207,109 +211,263 @@ struct OccOut {
     u64 *agg;              // get: [0] += hits, [1] += sum of the DATA bytes of the hits (nullable)
 };
 
-// One warp takes 32 records at a time and spreads their k-mers over its lanes, so that every lane runs
-// one table operation per step whatever the superkmer sizes are.
+// ---------------------------------------------------------------------------------------------
+// records_kernel: one warp takes 32 records at a time, stages them in shared memory and spreads their k-mers over
+// its lanes, so that every lane runs one table operation per step whatever the superkmer sizes are.
+//
+// A table operation is ONE probe (probe_once).  A lane whose probe did not settle its k-mer (slot taken by another
+// key, or claimed but not yet published) appends the k-mer to the warp's retry queue in shared memory and the warp
+// moves on; whenever the queue holds 32 entries the warp runs them as one full-width probe round.  The number of
+// probe rounds a warp executes is then the AVERAGE number of probes per k-mer, not the maximum over its 32 lanes,
+// and a lane never idles through another lane's collision chain.
+#define REC_QUEUE 64  // retry queue entries per warp (<= 31 left over + 32 from one round)
+
+struct KmerOp { u64 lo, hi, home, oi; u32 misc; bool active; };
+
+enum { PR_FOUND = 0, PR_NEW = 1, PR_ABSENT = 2, PR_NEXT = 3, PR_AGAIN = 4 };
+
+// one probe of slot s for (lo, hi, idx).  MODE_GET never writes.  PR_NEXT: the slot holds another key; PR_AGAIN: the
+// slot holds this k-mer's key words but its tag is not published yet — look at the same slot again.
+template <int KW, int MODE>
+__device__ __forceinline__ int probe_once(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 s, u32 &meta_out) {
+    typedef typename SlotOf<KW>::type S;
+    const u32 tag = idx + 1;
+    const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
+    S *p = reinterpret_cast<S *>(T.slots) + s;
+    u64 clo, chi;
+    u32 mt;
+    if (KW == 1) { ld_relaxed128(p, clo, chi); mt = (u32)chi; }
+    else { u64 w2, w3; ld_relaxed256(p, clo, chi, w2, w3); mt = (u32)w2; }
+    const bool empty = clo == STORE_EMPTY && (KW == 1 || chi == STORE_EMPTY);
+    if (empty) {
+        if (MODE == MODE_GET) return PR_ABSENT;
+        u64 olo, ohi = STORE_EMPTY;
+        if (KW == 1) olo = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo);
+        else cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
+        if (olo == STORE_EMPTY && ohi == STORE_EMPTY) {
+            atomicAdd(&p->meta, tag | add);
+            return PR_NEW;
+        }
+        // somebody else claimed the slot meanwhile: same key words -> wait for its tag, else move on
+        return (olo == lo && (KW == 1 || ohi == hi)) ? PR_AGAIN : PR_NEXT;
+    }
+    if (clo == lo && (KW == 1 || chi == hi)) {
+        const u32 t = mt & META_TAG_MASK;
+        if (t == 0) return PR_AGAIN;
+        if (t == tag) {
+            if (add) atomicAdd(&p->meta, add);
+            meta_out = mt;
+            return PR_FOUND;
+        }
+    }
+    return PR_NEXT;
+}
+
+template <int RW, int KW>
+struct RecWarpSmem {
+    static constexpr int PSTRIDE = 2 * RW + 3;  // odd: records of neighbouring lanes start in different banks; 3 zero words of slack
+    u32 payload[32 * PSTRIDE];
+    u64 gbase[32];
+    u64 occ[32];
+    u32 pack[32];  // exclusive prefix of n | n << 12 | idx0 << 20
+    // retry queue
+    u64 q_lo[REC_QUEUE];
+    u64 q_hi[KW == 2 ? REC_QUEUE : 1];
+    u64 q_home[REC_QUEUE];
+    u64 q_oi[REC_QUEUE];
+    u32 q_misc[REC_QUEUE];  // idx | first-of-record flag << 8 | probes << 16
+};
+
 template <int RW, int KW, int MODE>
 __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const u64 *__restrict__ recs, u64 n_recs,
                                                       StoreView T, OccOut O) {
+    __shared__ RecWarpSmem<RW, KW> smem[8];
+    RecWarpSmem<RW, KW> &S = smem[threadIdx.x >> 5];
+    constexpr int PSTRIDE = RecWarpSmem<RW, KW>::PSTRIDE;
     const int lane = threadIdx.x & 31;
+    const u32 lane_le = 0xffffffffu >> (31 - lane), lane_lt = lane_le >> 1;
     const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u64 n_warps = ((u64)gridDim.x * blockDim.x) >> 5;
     const u64 top_mask = rec_payload_mask_top(P);
     u32 new_keys = 0, new_recs = 0;
     u64 agg_hits = 0, agg_sum = 0;
-    for (u64 r0 = warp * 32; r0 < n_recs; r0 += n_warps * 32) {
-        const u64 ri = r0 + lane;
-        u64 w[RW];
-        int n = 0, idx0 = 0;
-        u64 bucket = 0, occ = 0, gbase = 0;
-        if (ri < n_recs) {
-            const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(recs + ri * RW);
-#pragma unroll
-            for (int i = 0; i < RW; i += 2) {
-                ulonglong2 v = __ldcs(src + (i >> 1));
-                w[i] = v.x; w[i + 1] = v.y;
-            }
-            rec_unpack_header(P, w[RW - 1], bucket, n, idx0);
-            w[RW - 1] &= top_mask;
-            // every k-mer of an inserted record ends up stored, so its bucket is in use: one bit per record (checked
-            // before the atomic), not one atomic per new k-mer
-            if (MODE != MODE_GET && T.bucket_bits) {
-                const u32 bit = 1u << (bucket & 31);
-                if (!(__ldg(T.bucket_bits + (bucket >> 5)) & bit)) atomicOr(T.bucket_bits + (bucket >> 5), bit);
-            }
-            // the minimizer m-mer of the record (nucleotides [idx0, idx0+m) of its first k-mer) places the whole superkmer
-            gbase = group_home(mw_extract64<RW, 3>(w, 2 * (n - 1 + idx0)) & P.m_mask, bucket, T.mask);
-            if (O.rec_occ) occ = O.rec_occ[ri];
-        } else {
-#pragma unroll
-            for (int i = 0; i < RW; i++) w[i] = 0;
-        }
-        // inclusive prefix sum of n over the warp
-        int incl = n;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int v = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += v;
-        }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        for (int c = 0; c < total; c += 32) {
-            const int o = c + lane;
-            // source lane = number of lanes whose inclusive prefix is <= o
-            int src = 0;
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1) {
-                int probe = __shfl_sync(0xffffffffu, incl, (src + step - 1) & 31);
-                if (src + step <= 32 && probe <= o) src += step;
-            }
-            const int src_l = src & 31;
-            // incl (<= 32 * 64), n (<= 64) and idx0 (< 64) of the source record in one shuffle
-            const u32 s_pack = __shfl_sync(0xffffffffu, (u32)incl | ((u32)n << 12) | ((u32)idx0 << 20), src_l);
-            const int s_incl = (int)(s_pack & 0xfffu), s_n = (int)((s_pack >> 12) & 0xffu), s_idx0 = (int)(s_pack >> 20);
-            const u64 s_occ = O.rec_occ ? __shfl_sync(0xffffffffu, occ, src_l) : 0ull;
-            const u64 s_gbase = __shfl_sync(0xffffffffu, gbase, src_l);
-            u64 pw[RW];
-#pragma unroll
-            for (int i = 0; i < RW; i++) pw[i] = __shfl_sync(0xffffffffu, w[i], src_l);
-            if (o < total) {
-                const int j = o - (s_incl - s_n);
-                u64 lo, hi;
-                record_kmer<RW, KW>(P, pw, s_n, j, lo, hi);
-                const u32 idx = (u32)(s_idx0 + j);
-                const u64 home = (s_gbase + idx) & T.mask;
-                u64 slot = ~0ull;
+    int qn = 0;  // queue length (warp-uniform)
+
+    // one probe round over the k-mers the lanes hold; unsettled ones go (back) to the queue
+    auto round = [&](bool active, u64 lo, u64 hi, u64 home, u64 oi, u32 misc) {
+        int res = PR_NEXT;
+        u32 mt = 0;
+        u64 slot = ~0ull;
+        if (active) {
+            const u32 idx = misc & 0xffu, probes = misc >> 16;
+            if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {  // the key that equals the empty pattern
+                slot = T.mask + 1 + idx;
                 if (MODE == MODE_GET) {
-                    u32 mt = 0;
-                    bool found = store_find<KW>(T, lo, hi, idx, home, slot, mt);
-                    if (found) { agg_hits++; agg_sum += mt >> 24; }
-                    if (O.rec_occ) {
-                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
-                        if (O.flags) O.flags[oi] = found;
-                        if (O.slots) O.slots[oi] = found ? slot : ~0ull;
-                        if (O.data) {
-                            if (T.data_size == 1) O.data[oi] = found ? (unsigned char)(mt >> 24) : 0;
-                            else for (u32 q = 0; q < T.data_size; q++)
-                                O.data[oi * T.data_size + q] = found ? T.data[slot * T.data_size + q] : 0;
-                        }
-                    }
+                    mt = ld_cg32(T.special + idx);
+                    res = (mt & META_TAG_MASK) == idx + 1 ? PR_FOUND : PR_ABSENT;
                 } else {
-                    const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
-                    int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
-                    if (res == 1) {
-                        new_keys++;
-                        if (j == 0) new_recs++;
-                    } else if (res < 0) {
-                        store_park(T, lo, hi, idx, add);
+                    u32 old = atomicAdd(T.special + idx, MODE == MODE_COUNT ? META_COUNT_ONE : 0u);
+                    res = PR_FOUND;
+                    if ((old & META_TAG_MASK) == 0) res = (atomicOr(T.special + idx, idx + 1) & META_TAG_MASK) == 0 ? PR_NEW : PR_FOUND;
+                }
+            } else if (probes >= STORE_MAX_PROBE) {
+                res = PR_ABSENT;  // probe limit: parked (insert) / absent (get)
+                if (MODE != MODE_GET) store_park(T, lo, hi, idx, MODE == MODE_COUNT ? META_COUNT_ONE : 0u);
+            } else {
+                slot = probe_slot(home, lo, KW == 1 ? 0 : hi, idx, probes, T.mask);
+                res = probe_once<KW, MODE>(T, lo, hi, idx, slot, mt);
+            }
+        }
+        const bool again = active && res >= PR_NEXT;
+        const u32 am = __ballot_sync(0xffffffffu, again);
+        if (again) {
+            const int q = qn + __popc(am & lane_lt);
+            S.q_lo[q] = lo;
+            if (KW == 2) S.q_hi[q] = hi;
+            S.q_home[q] = home;
+            S.q_oi[q] = oi;
+            S.q_misc[q] = res == PR_NEXT ? misc + (1u << 16) : misc;
+        }
+        qn += __popc(am);
+        if (active && !again) {
+            const bool hit = res == PR_FOUND;
+            if (MODE == MODE_GET) {
+                if (hit) { agg_hits++; agg_sum += mt >> 24; }
+                if (O.rec_occ) {
+                    if (O.flags) O.flags[oi] = hit;
+                    if (O.slots) O.slots[oi] = hit ? slot : ~0ull;
+                    if (O.data) {
+                        if (T.data_size == 1) O.data[oi] = hit ? (unsigned char)(mt >> 24) : 0;
+                        else for (u32 q = 0; q < T.data_size; q++)
+                            O.data[oi * T.data_size + q] = hit ? T.data[slot * T.data_size + q] : 0;
                     }
-                    if (O.rec_occ) {
-                        u64 oi = (s_occ >> 1) + ((s_occ & 1) ? (u64)(s_n - 1 - j) : (u64)j);
-                        if (O.flags) O.flags[oi] = res == 1;
-                        if (O.slots) O.slots[oi] = res < 0 ? ~0ull : slot;
-                    }
+                }
+            } else {
+                if (res == PR_NEW) {
+                    new_keys++;
+                    if (misc & 0x100u) new_recs++;
+                }
+                if (O.rec_occ) {
+                    if (O.flags) O.flags[oi] = res == PR_NEW;
+                    if (O.slots) O.slots[oi] = res == PR_ABSENT ? ~0ull : slot;
                 }
             }
         }
+    };
+    // run the newest 32 (or all, if fewer) queued k-mers as one round
+    auto retry = [&]() {
+        const int take = qn < 32 ? qn : 32;
+        qn -= take;
+        __syncwarp();
+        const bool active = lane < take;
+        u64 lo = 0, hi = 0, home = 0, oi = 0;
+        u32 misc = 0;
+        if (active) {
+            const int q = qn + lane;
+            lo = S.q_lo[q];
+            if (KW == 2) hi = S.q_hi[q];
+            home = S.q_home[q];
+            oi = S.q_oi[q];
+            misc = S.q_misc[q];
+        }
+        __syncwarp();
+        round(active, lo, hi, home, oi, misc);
+    };
+
+    for (u64 r0 = warp * 32; r0 < n_recs; r0 += n_warps * 32) {
+        const u64 ri = r0 + lane;
+        int n = 0;
+        __syncwarp();  // the lanes are done with the previous group's staging
+        {
+            u64 w[RW];
+            int idx0 = 0;
+            u64 bucket = 0, gbase = 0;
+            if (ri < n_recs) {
+                const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(recs + ri * RW);
+#pragma unroll
+                for (int i = 0; i < RW; i += 2) {
+                    ulonglong2 v = __ldcs(src + (i >> 1));
+                    w[i] = v.x; w[i + 1] = v.y;
+                }
+                rec_unpack_header(P, w[RW - 1], bucket, n, idx0);
+                w[RW - 1] &= top_mask;
+                // every k-mer of an inserted record ends up stored, so its bucket is in use: one bit per record (checked
+                // before the atomic), not one atomic per new k-mer
+                if (MODE != MODE_GET && T.bucket_bits) {
+                    const u32 bit = 1u << (bucket & 31);
+                    if (!(__ldg(T.bucket_bits + (bucket >> 5)) & bit)) atomicOr(T.bucket_bits + (bucket >> 5), bit);
+                }
+                // the minimizer m-mer of the record (nucleotides [idx0, idx0+m) of its first k-mer) places the whole superkmer
+                gbase = group_home(mw_extract64<RW, 3>(w, 2 * (n - 1 + idx0)) & P.m_mask, bucket, T.mask);
+                S.occ[lane] = O.rec_occ ? O.rec_occ[ri] : 0ull;
+            } else {
+#pragma unroll
+                for (int i = 0; i < RW; i++) w[i] = 0;
+            }
+            u32 *pp = S.payload + lane * PSTRIDE;
+#pragma unroll
+            for (int i = 0; i < RW; i++) { pp[2 * i] = (u32)w[i]; pp[2 * i + 1] = (u32)(w[i] >> 32); }
+            pp[2 * RW] = 0; pp[2 * RW + 1] = 0; pp[2 * RW + 2] = 0;
+            S.gbase[lane] = gbase;
+            // inclusive prefix sum of n over the warp
+            int incl = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            n = incl - n;  // from here on: the exclusive prefix = first output slot of this lane's record
+            S.pack[lane] = (u32)n | ((u32)(incl - n) << 12) | ((u32)idx0 << 20);
+        }
+        const int excl = n;
+        const int total = __shfl_sync(0xffffffffu, excl + (int)((S.pack[lane] >> 12) & 0xffu), 31);
+        __syncwarp();
+        // k-mer of output slot c + lane; its home sector is requested (L2 prefetch) one step ahead of its probe
+        auto prepare = [&](int c) -> KmerOp {
+            KmerOp K;
+            K.lo = 0; K.hi = 0; K.home = 0; K.oi = 0; K.misc = 0;
+            const int o = c + lane;
+            // source record of output slot o = the last record that starts at or before o: records are in lane order,
+            // so it is (records starting before c) + (records starting in [c, o]) - 1
+            const u32 starts = __reduce_or_sync(0xffffffffu, (excl >= c && excl < c + 32) ? 1u << (excl - c) : 0u);
+            const int before = __popc(__ballot_sync(0xffffffffu, excl < c));
+            K.active = o < total;
+            if (K.active) {
+                const int src = before + __popc(starts & lane_le) - 1;
+                const u32 pk = S.pack[src];
+                const int s_n = (int)((pk >> 12) & 0xffu), j = o - (int)(pk & 0xfffu);
+                const u32 idx = (pk >> 20) + (u32)j;
+                // k-mer j (emission order) of the record: bits [2(n-1-j), 2(n-1-j) + 2k) of its payload
+                const int sh = 2 * (s_n - 1 - j);
+                const u32 *pp = S.payload + src * PSTRIDE + (sh >> 5);
+                u32 x[2 * KW + 1];
+#pragma unroll
+                for (int i = 0; i <= 2 * KW; i++) x[i] = pp[i];
+                u32 y[2 * KW];
+#pragma unroll
+                for (int i = 0; i < 2 * KW; i++) y[i] = __funnelshift_r(x[i], x[i + 1], sh & 31);
+                K.lo = ((u64)y[0] | ((u64)y[1] << 32)) & P.kmask_lo;
+                if (KW == 2) K.hi = ((u64)y[2] | ((u64)y[3] << 32)) & P.kmask_hi;
+                K.home = (S.gbase[src] + idx) & T.mask;
+                if (O.rec_occ) {
+                    const u64 so = S.occ[src];
+                    K.oi = (so >> 1) + ((so & 1) ? (u64)(s_n - 1 - j) : (u64)j);
+                }
+                K.misc = idx | (j == 0 ? 0x100u : 0u);
+                typedef typename SlotOf<KW>::type SL;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const SL *>(T.slots) + K.home));
+            }
+            return K;
+        };
+        KmerOp nx = prepare(0);
+        for (int c = 0; c < total; c += 32) {
+            const KmerOp cur = nx;
+            if (c + 32 < total) nx = prepare(c + 32);
+            round(cur.active, cur.lo, cur.hi, cur.home, cur.oi, cur.misc);
+            while (qn >= 32) retry();
+        }
     }
+    while (qn > 0) retry();
     if (MODE == MODE_GET && O.agg) {
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
