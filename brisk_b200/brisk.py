@@ -23,6 +23,7 @@ KMER_DT = np.dtype([("lo", "<u8"), ("hi", "<u8"), ("idx", "u1"), ("pad", "u1", (
 NO_SLOT = np.uint64(0xFFFFFFFFFFFFFFFF)
 F_MANAGED = 1
 F_LITERAL_DECYCLE = 2
+F_SYNC_INSERT = 4
 
 
 class BriskError(RuntimeError):

@@ -69,6 +69,9 @@ struct brisk_handle {
     cudaEvent_t ev[6] = {};
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t chunk_ev[BRISK_MAX_CHUNKS] = {};
+    cudaEvent_t offsets_ev = nullptr;
+    bool pending_settle = false;  // a count / insert call left its store kernel running: settle() before the table is used again
+    bool timing_dirty = false;    // stage times of the last call not read back yet
     float last_ms[5] = {0, 0, 0, 0, 0};
     uint32_t last_launches = 0;
     // store
@@ -256,6 +259,7 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
     CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < BRISK_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&h->chunk_ev[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->offsets_ev, cudaEventDisableTiming));
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
     CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
@@ -321,6 +325,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaFree(h->d_rec_count);
     for (int i = 0; i < 6; i++) cudaEventDestroy(h->ev[i]);
     for (int i = 0; i < BRISK_MAX_CHUNKS; i++) cudaEventDestroy(h->chunk_ev[i]);
+    if (h->offsets_ev) cudaEventDestroy(h->offsets_ev);
     cudaStreamDestroy(h->copy_stream);
     cudaStreamDestroy(h->own_stream);
     delete h;
@@ -351,7 +356,12 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
     } else {
         total = offsets[n_reads];
         CK(h->d_offsets.ensure((n_reads + 1) * sizeof(uint64_t)));
-        CK(cudaMemcpyAsync(h->d_offsets.p, offsets, (n_reads + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+        // on the copy stream, ahead of the bases: the handle's stream may still be busy with the previous call's store
+        // kernel (which does not read the offsets), and a copy queued behind it would reach the copy engine after all
+        // the chunk copies of this call
+        CK(cudaMemcpyAsync(h->d_offsets.p, offsets, (n_reads + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+        CK(cudaEventRecord(h->offsets_ev, h->copy_stream));
+        CK(cudaStreamWaitEvent(h->stream, h->offsets_ev, 0));
         B.d_offsets = (const u64 *)h->d_offsets.p;
     }
     B.total_bytes = total;
@@ -437,14 +447,14 @@ __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *
 static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, uint64_t &n_recs, uint64_t &n_occ,
                            size_t c0 = 0, size_t c1 = ~(size_t)0) {
     n_recs = 0;
-    n_occ = 0;
+    if (c0 == 0) n_occ = 0;  // the occurrence index of the whole batch is built with its first chunk
     c1 = std::min(c1, B.chunk_first.size() - 1);  // chunks [c0, c1) of the batch (default: all of it)
     if (B.n_reads == 0) {
         CK(cudaEventRecord(h->ev[1], h->stream));
         return BRISK_OK;
     }
     const int RW = h->P.rec_words;
-    if (with_occ) {
+    if (with_occ && c0 == 0) {
         CK(h->d_cnt.ensure((B.n_reads + 1) * sizeof(uint64_t)));
         CK(h->d_kmer_base.ensure((B.n_reads + 1) * sizeof(uint64_t)));
         unsigned blocks = (unsigned)((B.n_reads + 1 + 255) / 256);
@@ -787,7 +797,17 @@ static int settle(brisk_handle *h) {
     return fail(BRISK_E_FULL, "bucket store could not absorb the parked inserts");
 }
 
+// count / insert calls without per-occurrence outputs return once their input has been consumed; their store kernel
+// is settled (counters read back, parked inserts replayed) when the handle is used next
+static int settle_pending(brisk_handle *h) {
+    if (!h->pending_settle) return BRISK_OK;
+    h->pending_settle = false;
+    return settle(h);
+}
+#define SETTLE_PENDING(h) do { int prc_ = settle_pending(h); if (prc_) return prc_; } while (0)
+
 static void finish_timing(brisk_handle *h) {
+    h->timing_dirty = false;
     // ev: 0 start/pack begin, 1 pack end, 2 enumerate end, 3 partition end, 4 insert end
     cudaEventSynchronize(h->ev[4]);
     for (int i = 0; i < 4; i++) cudaEventElapsedTime(&h->last_ms[i], h->ev[i], h->ev[i + 1]);
@@ -805,36 +825,10 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     ReadBatch B;
     int rc = stage_reads(h, bases, offsets, n_reads, B);
     if (rc) return rc;
+    SETTLE_PENDING(h);  // after staging: this call's host->device copies run while the previous store kernel finishes
     const bool with_occ = slots || flags || data_out;
     const bool sharded = h->comm && h->comm->n > 1;
-    // (A variant that also ran the store kernel chunk by chunk was measured: no gain — the e2e step is bound by the
-    // 541 MB of H2D per step at about 26 GB/s on this box — and it made the stage timings inseparable; not kept.)
     uint64_t n_recs = 0, n_occ = 0;
-    rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
-    if (rc) return rc;
-    CK(cudaEventRecord(h->ev[2], h->stream));
-    Exchange X;
-    X.recs = (const u64 *)h->d_recs.p;
-    X.n = n_recs;
-    if (sharded) {
-        rc = exchange_records(h, n_recs, with_occ, X);
-        if (rc) return rc;
-    }
-    // Records in table-region order: the store kernel then walks the table region by region (L2 keeps the slots a
-    // batch revisits, the TLB sees one region at a time).  Occurrence tags travel with their records.
-    const u64 *tags = !with_occ ? nullptr : sharded ? (const u64 *)h->d_recv_occ.p : (const u64 *)h->d_rec_occ.p;
-    if (h->region_sort && X.n >= 4096) {
-        DevBuf &dst = sharded ? h->d_recs : h->d_send, &dst_occ = sharded ? h->d_rec_occ : h->d_send_occ;
-        rc = partition_records(h, X.recs, tags, X.n, STORE_REGIONS, 1, dst, dst_occ);
-        if (rc) return rc;
-        X.recs = (const u64 *)dst.p;
-        if (tags) tags = (const u64 *)dst_occ.p;
-    }
-    CK(cudaEventRecord(h->ev[3], h->stream));
-    if (mode != MODE_GET) {
-        rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes);
-        if (rc) return rc;
-    }
     OccOut O;
     O.rec_occ = nullptr; O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
     if (agg_out) {
@@ -842,47 +836,92 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         O.agg = h->counters + 5;
     }
     // per-occurrence outputs go through device staging when the caller's buffers are on the host
-    bool s_dev = is_device_ptr(slots), f_dev = is_device_ptr(flags), d_dev = is_device_ptr(data_out);
+    const bool s_dev = is_device_ptr(slots), f_dev = is_device_ptr(flags), d_dev = is_device_ptr(data_out);
     u64 *o_slots = nullptr;
     unsigned char *o_flags = nullptr, *o_data = nullptr;
-    if (slots) {
-        if (s_dev) o_slots = (u64 *)slots;
-        else { CK(h->d_out_slots.ensure((n_occ + 1) * sizeof(uint64_t))); o_slots = (u64 *)h->d_out_slots.p; }
-    }
-    if (flags) {
-        if (f_dev) o_flags = flags;
-        else { CK(h->d_out_flags.ensure(n_occ + 1)); o_flags = (unsigned char *)h->d_out_flags.p; }
-    }
-    if (data_out) {
-        if (d_dev) o_data = (unsigned char *)data_out;
-        else { CK(h->d_out_data.ensure((n_occ + 1) * h->data_size)); o_data = (unsigned char *)h->d_out_data.p; }
-    }
+    auto stage_outputs = [&]() -> int {  // needs n_occ (known once the first chunk is enumerated)
+        if (slots) {
+            if (s_dev) o_slots = (u64 *)slots;
+            else { CK(h->d_out_slots.ensure((n_occ + 1) * sizeof(uint64_t))); o_slots = (u64 *)h->d_out_slots.p; }
+        }
+        if (flags) {
+            if (f_dev) o_flags = flags;
+            else { CK(h->d_out_flags.ensure(n_occ + 1)); o_flags = (unsigned char *)h->d_out_flags.p; }
+        }
+        if (data_out) {
+            if (d_dev) o_data = (unsigned char *)data_out;
+            else { CK(h->d_out_data.ensure((n_occ + 1) * h->data_size)); o_data = (unsigned char *)h->d_out_data.p; }
+        }
+        return BRISK_OK;
+    };
+    // Records in table-region order: the store kernel then walks the table region by region (L2 keeps the slots a
+    // batch revisits, the TLB sees one region at a time).  Occurrence tags travel with their records.
+    auto by_region = [&](const u64 *&recs, const u64 *&tags, uint64_t n, DevBuf &dst, DevBuf &dst_occ) -> int {
+        if (!h->region_sort || n < 4096) return BRISK_OK;
+        int prc = partition_records(h, recs, tags, n, STORE_REGIONS, 1, dst, dst_occ);
+        if (prc) return prc;
+        recs = (const u64 *)dst.p;
+        if (tags) tags = (const u64 *)dst_occ.p;
+        return BRISK_OK;
+    };
     DevBuf back_slots, back_flags, back_data;
-    if (!sharded) {
-        O.rec_occ = tags;
-        O.slots = o_slots; O.flags = o_flags; O.data = o_data;
-    } else if (with_occ) {
-        // the owner writes its answers in arrival order; they travel back and are put in read order below
-        const uint64_t n_ret = X.recv_occ_start[h->comm->n];
-        O.rec_occ = tags;
-        if (slots) { CK(h->d_ret_slots.ensure((n_ret + 1) * sizeof(uint64_t))); O.slots = (u64 *)h->d_ret_slots.p; }
-        if (flags) { CK(h->d_ret_flags.ensure(n_ret + 1)); O.flags = (unsigned char *)h->d_ret_flags.p; }
-        if (data_out) { CK(h->d_ret_data.ensure((n_ret + 1) * h->data_size)); O.data = (unsigned char *)h->d_ret_data.p; }
-    }
-    CK(launch_records(h, mode, X.recs, X.n, O));
-    if (X.n) h->last_launches++;
-    if (sharded && with_occ) {
-        rc = return_results(h, X, n_recs, slots != nullptr, flags != nullptr, data_out != nullptr, back_slots, back_flags, back_data,
-                            o_slots, o_flags, o_data);
+    // (Running the store kernel chunk by chunk as the host copies arrive was measured twice: slower.  Eight small
+    // launches lose the region order's locality (each chunk walks the whole table) and the enumerate launches lose
+    // to wave quantisation; the call went from 8.4-8.8 ms to 9.1-9.9 ms.  Instead count / insert calls return once
+    // their input is consumed, and the NEXT call's host->device copy overlaps this call's store kernel.)
+    {
+        rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
         if (rc) return rc;
+        CK(cudaEventRecord(h->ev[2], h->stream));
+        Exchange X;
+        X.recs = (const u64 *)h->d_recs.p;
+        X.n = n_recs;
+        if (sharded) {
+            rc = exchange_records(h, n_recs, with_occ, X);
+            if (rc) return rc;
+        }
+        const u64 *tags = !with_occ ? nullptr : sharded ? (const u64 *)h->d_recv_occ.p : (const u64 *)h->d_rec_occ.p;
+        rc = by_region(X.recs, tags, X.n, sharded ? h->d_recs : h->d_send, sharded ? h->d_rec_occ : h->d_send_occ);
+        if (rc) return rc;
+        CK(cudaEventRecord(h->ev[3], h->stream));
+        if (mode != MODE_GET) {
+            rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes);
+            if (rc) return rc;
+        }
+        rc = stage_outputs();
+        if (rc) return rc;
+        if (!sharded) {
+            O.rec_occ = tags;
+            O.slots = o_slots; O.flags = o_flags; O.data = o_data;
+        } else if (with_occ) {
+            // the owner writes its answers in arrival order; they travel back and are put in read order below
+            const uint64_t n_ret = X.recv_occ_start[h->comm->n];
+            O.rec_occ = tags;
+            if (slots) { CK(h->d_ret_slots.ensure((n_ret + 1) * sizeof(uint64_t))); O.slots = (u64 *)h->d_ret_slots.p; }
+            if (flags) { CK(h->d_ret_flags.ensure(n_ret + 1)); O.flags = (unsigned char *)h->d_ret_flags.p; }
+            if (data_out) { CK(h->d_ret_data.ensure((n_ret + 1) * h->data_size)); O.data = (unsigned char *)h->d_ret_data.p; }
+        }
+        CK(launch_records(h, mode, X.recs, X.n, O));
+        if (X.n) h->last_launches++;
+        if (sharded && with_occ) {
+            rc = return_results(h, X, n_recs, slots != nullptr, flags != nullptr, data_out != nullptr, back_slots, back_flags, back_data,
+                                o_slots, o_flags, o_data);
+            if (rc) return rc;
+        }
+        if (sharded && agg_out)  // every rank gets the totals of the whole query batch
+            NCK(g_nccl.AllReduce(h->counters + 5, h->counters + 5, 2, ncclUint64, ncclSum, h->comm->comm, h->stream));
     }
-    if (sharded && agg_out)  // every rank gets the totals of the whole query batch
-        NCK(g_nccl.AllReduce(h->counters + 5, h->counters + 5, 2, ncclUint64, ncclSum, h->comm->comm, h->stream));
     CK(cudaEventRecord(h->ev[4], h->stream));
     if (slots && !s_dev) CK(cudaMemcpyAsync(slots, o_slots, n_occ * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     if (flags && !f_dev) CK(cudaMemcpyAsync(flags, o_flags, n_occ, cudaMemcpyDeviceToHost, h->stream));
     if (data_out && !d_dev) CK(cudaMemcpyAsync(data_out, o_data, n_occ * h->data_size, cudaMemcpyDeviceToHost, h->stream));
     if (agg_out) CK(cudaMemcpyAsync(agg_out, h->counters + 5, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    if (mode != MODE_GET && !with_occ && !(h->flags & BRISK_F_SYNC_INSERT)) {
+        // nothing to hand back and the input is consumed (enumeration was waited for): leave the store kernel running
+        h->pending_settle = true;
+        h->timing_dirty = true;
+        return BRISK_OK;
+    }
     if (mode != MODE_GET) {
         rc = settle(h);
     } else {
@@ -922,6 +961,7 @@ extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
     ReadBatch B;
@@ -951,6 +991,7 @@ extern "C" int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
     ReadBatch B;
@@ -980,6 +1021,7 @@ static int run_kmers(brisk_handle *h, const brisk_kmer *kmers, uint64_t n, int m
     if (n && !kmers) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->last_launches = 0;
     if (n == 0) return BRISK_OK;
     const KmerIn *d_k;
@@ -1031,7 +1073,12 @@ extern "C" int brisk_get_kmers(brisk_t *h, const brisk_kmer *kmers, uint64_t n, 
 }
 
 extern "C" void *brisk_data_ptr(brisk_t *h, uint64_t slot) {
-    if (!h || slot == BRISK_NO_SLOT || slot >= h->cap + 64) return nullptr;
+    if (!h) return nullptr;
+    if (h->pending_settle) {  // the caller is about to dereference the pointer: the store has to be at rest
+        std::lock_guard<std::recursive_mutex> lock(h->mu);
+        if (cudaSetDevice(h->device) != cudaSuccess || settle_pending(h) != BRISK_OK) return nullptr;
+    }
+    if (slot == BRISK_NO_SLOT || slot >= h->cap + 64) return nullptr;
     if (h->data_size == 1) {
         if (slot >= h->cap) return (unsigned char *)(h->special + (slot - h->cap)) + 3;
         size_t off = slot * slot_bytes(h) + (h->P.key_words == 1 ? offsetof(Slot1, meta) : offsetof(Slot2, meta)) + 3;
@@ -1044,6 +1091,7 @@ extern "C" int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     CK(cudaStreamSynchronize(h->stream));
     if (n) *n = h->n_keys;
     if (!keys && !data) return BRISK_OK;
@@ -1106,6 +1154,7 @@ extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint
     if (nk >= (1ull << 32)) return fail(BRISK_E_CAPACITY, "ordered dump handles fewer than 2^32 k-mers per shard");
     if (nk == 0) return BRISK_OK;
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     DevBuf ukeys, udata, lo, hi, top, tmpk, perm, perm2, cubtmp, okeys, odata;
     auto cleanup = [&]() { for (DevBuf *b : {&ukeys, &udata, &lo, &hi, &top, &tmpk, &perm, &perm2, &cubtmp, &okeys, &odata}) b->release(); };
     auto body = [&]() -> int {
@@ -1157,6 +1206,7 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     uint64_t nb = 0;
     CK(cudaMemsetAsync(h->counters + 4, 0, sizeof(uint64_t), h->stream));
     unsigned blocks = (unsigned)std::min<uint64_t>((h->bitmap_words + 255) / 256, 148 * 16);
@@ -1185,6 +1235,7 @@ extern "C" int brisk_reserve(brisk_t *h, uint64_t n_keys) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->hint = std::max(h->hint, n_keys);
     int rc = grow_to(h, pow2ceil(std::max<uint64_t>(n_keys * 2, 1u << 16)));
     if (rc) return rc;
@@ -1193,12 +1244,17 @@ extern "C" int brisk_reserve(brisk_t *h, uint64_t n_keys) {
 }
 extern "C" int brisk_capacity(brisk_t *h, uint64_t *slots) {
     if (!h || !slots) return fail(BRISK_E_PARAM, "null argument");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     *slots = h->cap;
     return BRISK_OK;
 }
 extern "C" int brisk_sync(brisk_t *h) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     CK(cudaStreamSynchronize(h->stream));
     return BRISK_OK;
 }
@@ -1206,12 +1262,18 @@ extern "C" int brisk_set_stream(brisk_t *h, void *stream) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     CK(cudaStreamSynchronize(h->stream));
     h->stream = stream ? (cudaStream_t)stream : h->own_stream;
     return BRISK_OK;
 }
 extern "C" int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    if (h->timing_dirty) {
+        CK(cudaSetDevice(h->device));
+        finish_timing(h);
+    }
     if (ms) memcpy(ms, h->last_ms, sizeof(h->last_ms));
     if (n_launches) *n_launches = h->last_launches;
     return BRISK_OK;
@@ -1261,6 +1323,7 @@ extern "C" int brisk_parse_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     uint64_t nb = 0, nr = 0;
     int rc = parse_fasta(h, text, n_bytes, nb, nr);
     if (rc) return rc;
@@ -1285,6 +1348,7 @@ extern "C" int brisk_count_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     uint64_t nb = 0, nr = 0;
     int rc = parse_fasta(h, text, n_bytes, nb, nr);
     if (rc) return rc;
@@ -1296,6 +1360,7 @@ extern "C" int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     if (n_bytes && !text) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     uint64_t nb = 0, nr = 0;
     int rc = parse_fasta(h, text, n_bytes, nb, nr);
     if (rc) return rc;
@@ -1310,6 +1375,7 @@ extern "C" int brisk_partition_reads(brisk_t *h, const char *bases, const uint64
     if (!starts) return fail(BRISK_E_PARAM, "starts is null");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->last_launches = 0;
     if (rec_words) *rec_words = (uint32_t)h->P.rec_words;
     ReadBatch B;
@@ -1341,6 +1407,7 @@ extern "C" int brisk_apply_records(brisk_t *h, const uint64_t *recs, uint64_t n_
     if (op < 0 || op > 2) return fail(BRISK_E_PARAM, "op must be 0 (count), 1 (insert) or 2 (get)");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     h->last_launches = 0;
     const int RW = h->P.rec_words;
     const u64 *d_r = (const u64 *)recs;
@@ -1404,6 +1471,7 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
     if (!g_nccl.load()) return fail(BRISK_E_COMM, g_nccl.error);
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
     ncclUniqueId u;
     memcpy(&u, id, 128);
     Comm *c = new Comm();

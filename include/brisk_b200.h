@@ -45,6 +45,10 @@ typedef struct brisk_handle brisk_t;
 /* flags for brisk_create */
 #define BRISK_F_MANAGED 1u        /* store in cudaMallocManaged memory: brisk_data_ptr() is host-dereferenceable */
 #define BRISK_F_LITERAL_DECYCLE 2u /* debug: evaluate DecyclingSet::memDouble literally for every m-mer */
+#define BRISK_F_SYNC_INSERT 4u     /* brisk_count_reads / brisk_insert_reads return only when the store kernel has finished
+                                    * (default: they return once the input buffers may be reused; the insertion completes in
+                                    * stream order before any later call on the handle reads the store, and a store-full
+                                    * error of such a call is reported by the next call or by brisk_sync) */
 
 /* one k-mer as the reference's kmer_full carries it */
 typedef struct {

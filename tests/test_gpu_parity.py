@@ -375,3 +375,35 @@ def test_ordered_dump_walks_buckets_in_id_order(name):
         if prev is not None:
             assert prev < key
         prev = key
+
+
+@pytest.mark.gpu
+def test_count_returns_early_and_every_reader_sees_the_finished_store():
+    """brisk_count_reads returns once its input is consumed (include/brisk_b200.h, BRISK_F_SYNC_INSERT); whatever is
+    called next on the handle — query, stats, dump, capacity, another count over a reused host buffer — must see the
+    completed insertion.  Same batches through a BRISK_F_SYNC_INSERT handle give the same dump."""
+    from brisk_b200 import Brisk, Parameters, synth
+    from brisk_b200.brisk import F_SYNC_INSERT
+    k, m, b, L = 31, 15, 12, 150
+    gen = synth.genome(200_000, 11)
+    n = 20_000
+    host = np.empty(n * L, np.uint8)
+    offs = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
+    dumps = []
+    for flags in (0, F_SYNC_INSERT):
+        idx = Brisk(Parameters(k, m, b), flags=flags)  # no capacity hint: the store grows while batches are in flight
+        for j in range(4):
+            host[:] = synth.reads(gen, L, 11, j * n, n).reshape(-1)  # the buffer of the previous call is overwritten
+            idx.count_reads(host, offs)
+            if j == 1:
+                hits, total = idx.query_reads(host, offs)
+                assert hits == n * (L - k + 1)
+            if j == 2:
+                assert idx.stats()["nb_kmers"] > 0
+        lo, hi, ix, cnt = idx.dump()
+        order = np.lexsort((ix, hi, lo))
+        dumps.append((lo[order], hi[order], ix[order], cnt[order]))
+        idx.close()
+    for a, c in zip(dumps[0], dumps[1]):
+        assert np.array_equal(a, c)
+    assert int(dumps[0][3].astype(np.int64).sum()) == 4 * n * (L - k + 1)  # 60x coverage: far from the uint8 wrap
