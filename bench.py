@@ -201,6 +201,7 @@ def run_ours(args):
             acc["store_ms"] += t["store_ms"]
             acc["enum_ms"] += t["enumerate_ms"]
             acc["pack_ms"] += t["pack_ms"]
+            acc["part_ms"] += t["partition_ms"]
             acc["launches"] += t["launches"]
         if j > 0:
             hits, total = idx.query_reads(batches[j - 1], offsets)
@@ -209,6 +210,7 @@ def run_ours(args):
                 acc["launches"] += tq["launches"]
                 acc["q_enum_ms"] += tq["enumerate_ms"]
                 acc["q_store_ms"] += tq["store_ms"]
+                acc["part_ms"] += tq["partition_ms"]
             acc["hits"] += hits
 
     def barrier():
@@ -219,7 +221,7 @@ def run_ours(args):
 
     def timed(batches, offsets, stage_times=True):
         idx = make_index()
-        acc = dict(store_ms=0.0, enum_ms=0.0, pack_ms=0.0, launches=0, hits=0, q_enum_ms=0.0, q_store_ms=0.0)
+        acc = dict(store_ms=0.0, enum_ms=0.0, pack_ms=0.0, part_ms=0.0, launches=0, hits=0, q_enum_ms=0.0, q_store_ms=0.0)
         wacc = dict(acc)
         # warm-up on the first batches, then a fresh store for the timed steps
         for j in range(min(warmup, n_batches)):
@@ -277,12 +279,14 @@ def run_ours(args):
                 "ms_per_launch": ms, "launches_per_step": launches_per_step,
                 "share_of_step": launches_per_step * ms / (ms_dev / steps), "note": note}
 
-    r_enum = roof("enumerate_kernel<4,ringless> (pack excluded)", enum_bytes, enum_ms, 2, 0.2959e9,
-                  "issue-bound (81 % issue-active in profiles/r1g_summary.md), not HBM-bound; traffic from the ncu capture "
-                  "of the same 2^20-read batch shape")
-    r_ins = roof("records_kernel<4,2,COUNT> (insert/count)", ins_bytes, ins_ms, 1, None,
-                 "random 32-byte sectors: 65 B of DRAM traffic per occurrence in profiles/r1g_summary.md (12.9 GB per launch on "
-                 "the 10 Mbp profiling genome; not captured at the full 17 GB table)")
+    r_enum = roof("enumerate_kernel<4,ringless> (pack excluded)", enum_bytes, enum_ms, 2, 0.2942e9,
+                  "issue-bound (81 % issue-active, 3.05 G warp instructions per launch in profiles/r1i_summary.md), not "
+                  "HBM-bound; traffic from the ncu capture of the same 2^20-read batch shape")
+    r_ins = roof("records_kernel<4,2,COUNT> (insert/count)", ins_bytes, ins_ms, 1, 12.33e9,
+                 "one 32-byte slot read and written back per occurrence: 11.9-12.8 GB of DRAM traffic per launch at the full "
+                 "17 GB table (profiles/r1i_full_table.csv, 2.73-2.86 ms per launch = 4.4 TB/s, 67 % of the measured HBM "
+                 "peak); the 18 B per occurrence of SURVEY.md 8(d) assumes byte-granular access, a 32-byte sector is what "
+                 "HBM moves")
     dominant, other = (r_enum, r_ins) if r_enum["share_of_step"] >= r_ins["share_of_step"] else (r_ins, r_enum)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
@@ -297,6 +301,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": world * (32 + 16 + 8 + 8)},
         "gpu_launches": acc_dev["launches"],
         "stage_ms_per_step": {"pack": acc_dev["pack_ms"] / steps, "enumerate": acc_dev["enum_ms"] / steps,
+                              "region_order": acc_dev["part_ms"] / steps,
                               "insert": acc_dev["store_ms"] / steps, "query_enumerate": acc_dev["q_enum_ms"] / steps,
                               "query_get": acc_dev["q_store_ms"] / steps},
         "roofline": dominant, "roofline_other": other,
