@@ -374,9 +374,10 @@ static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offse
         CK(h->d_bases.ensure(total + 16));
         B.d_bases = (const unsigned char *)h->d_bases.p;
         // chunks of about total / 8 bytes on read boundaries (the host offsets are at hand), copied on the copy stream
-        const uint64_t want = std::max<uint64_t>(BRISK_MIN_CHUNK_BYTES, (total + BRISK_MAX_CHUNKS - 1) / BRISK_MAX_CHUNKS);
+        // (the last of 8 chunks is half the size of the others: what follows the last byte's arrival is its pack + enumerate)
+        const uint64_t want = std::max<uint64_t>(BRISK_MIN_CHUNK_BYTES, (2 * total + 2 * BRISK_MAX_CHUNKS - 2) / (2 * BRISK_MAX_CHUNKS - 1));
         uint64_t first = 0;
-        while (first < n_reads && B.chunk_first.size() < BRISK_MAX_CHUNKS) {
+        while (first < n_reads && B.chunk_first.size() < BRISK_MAX_CHUNKS + 1) {  // n chunks = n + 1 boundaries
             // last read whose end stays within `want` bytes of the chunk's start
             const uint64_t limit = offsets[first] + want;
             uint64_t lo = first + 1, hi = n_reads;
@@ -868,7 +869,9 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     // (Running the store kernel chunk by chunk as the host copies arrive was measured twice: slower.  Eight small
     // launches lose the region order's locality (each chunk walks the whole table) and the enumerate launches lose
     // to wave quantisation; the call went from 8.4-8.8 ms to 9.1-9.9 ms.  Instead count / insert calls return once
-    // their input is consumed, and the NEXT call's host->device copy overlaps this call's store kernel.)
+    // their input is consumed, and the NEXT call's host->device copy overlaps this call's store kernel.  Storing the
+    // first half of the chunks while the second half is on its way was measured too: the count call grows by what the
+    // next call saves, 15.6 -> 16.9 ms per step: the step is bound by its kernels, not by the copies.)
     {
         rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
         if (rc) return rc;
