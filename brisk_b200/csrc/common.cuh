@@ -137,12 +137,15 @@ __host__ __device__ __forceinline__ u64 bfc_hash_literal(const double *coef, dou
 // summation decides, so the class is always the one DecyclingSet::memDouble returns.
 __device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double *coef, const double2 *tab, u64 seq) {
     double Sr = 0, Si = 0;
-    u64 c = seq;
-    for (int g = 0; g < P.dec_groups; g++) {
-        const double2 e = tab[g * 64 + (int)(c & 63)];
-        Sr += e.x;
-        Si += e.y;
-        c >>= 6;
+    // m <= 32: at most 11 groups of 3 nucleotides.  Unrolled with constant table offsets: the loads of all groups
+    // issue back to back (a counted loop serialised them behind its own bookkeeping)
+#pragma unroll
+    for (int g = 0; g < 11; g++) {
+        if (g < P.dec_groups) {
+            const double2 e = tab[g * 64 + (int)((seq >> (6 * g)) & 63)];
+            Sr += e.x;
+            Si += e.y;
+        }
     }
     const double R = Si, R2 = fma(Sr, P.rot_s, Si * P.rot_c);
     if (fabs(fabs(R) - P.eps) < P.guard || fabs(fabs(R2) - P.eps) < P.guard) return dec_mem_double(coef, P.eps, seq, P.m);

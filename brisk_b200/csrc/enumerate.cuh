@@ -183,16 +183,17 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
         }
     };
 
+    static_assert(ENUM_SYNC_STEPS == 32, "one packed word per block of steps");
     for (u32 t0 = 0; t0 < maxL; t0 += ENUM_SYNC_STEPS) {
+        if (t0 < L) word = __ldg(pk + (t0 >> 5));  // the 32 bases of this block of steps
         for (u32 t = t0; t < t0 + ENUM_SYNC_STEPS; t++) {
             const bool active = t < L;
             u64 h = 0;
             bool rv = false;
             int need_kk = 0;  // k-1: seed get_minimizer (Kmers.cpp:533), k: the minimizer left the window (:551-562)
             const bool old_rev = rev;
-            if (t + 1 >= (u32)m) rslot = rslot + 1 == P.w ? 0 : rslot + 1;  // same t in every thread: uniform
+            if (RING && t + 1 >= (u32)m) rslot = rslot + 1 == P.w ? 0 : rslot + 1;  // same t in every thread: uniform
             if (active) {
-                if ((t & 31) == 0) word = __ldg(pk + (t >> 5));
                 const u32 code = (u32)(word >> 62);
                 word <<= 2;
                 const u32 leave = (u32)(f >> rshift) & 3u;
