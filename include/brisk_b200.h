@@ -77,7 +77,9 @@ int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const uint64_t *
                                  uint64_t *recs, uint64_t cap_recs, uint64_t *n_recs, uint32_t *rec_words, uint64_t *occ);
 
 /* count_sequence for every read (apps/counter.cpp:231-276): insert_superkmer (brisk/Brisk.hpp:123-147)
- * fused with the counter's update  new -> 1, else ++ (uint8 wrap, apps/counter.cpp:262-269). */
+ * fused with the counter's update  new -> 1, else ++ (uint8 wrap, apps/counter.cpp:262-269).
+ * Returns when `bases` / `offsets` may be reused; the insertion completes in stream order before any later call on the
+ * handle touches the store (see BRISK_F_SYNC_INSERT, brisk_sync). */
 int brisk_count_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads);
 
 /* insert_superkmer without touching DATA: slot of every k-mer occurrence in read order (k-mer i of

@@ -272,6 +272,9 @@ public:
     }
     // the GPU analogue of Brisk::reallocate (brisk/Brisk.hpp:88-97): make room for n_keys distinct k-mers
     void reserve(uint64_t n_keys) { brisk_check(brisk_reserve(menu, n_keys)); }
+    // count_reads / insert_reads return once their input is consumed; sync() waits for the store to be at rest and
+    // reports a deferred store-full error (every call that reads the store does the same implicitly)
+    void sync() { brisk_check(brisk_sync(menu)); }
 
     // ---- batched calls (flat read buffer + n_reads + 1 byte offsets; host or device pointers) ------------
     void count_reads(const char *bases, const uint64_t *offsets, uint64_t n_reads) {  // apps/counter.cpp:231-276 per read
