@@ -73,3 +73,12 @@ def test_decode_records_layout():
     (b, kmers), = decode_records(rec, p)
     assert b == bucket and [i for _, i in kmers] == [5, 6, 7]
     assert kmers[0][0] == seq >> 4 and kmers[2][0] == seq & ((1 << 62) - 1)
+
+
+def test_create_flags_match_the_header():
+    """the BRISK_F_* values of include/brisk_b200.h and the Python mirror are the same numbers"""
+    import re
+    from brisk_b200 import brisk as B
+    text = open(os.path.join(os.path.dirname(__file__), "..", "include", "brisk_b200.h")).read()
+    flags = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define BRISK_F_(\w+)\s+(\d+)u", text)}
+    assert flags == {"MANAGED": B.F_MANAGED, "LITERAL_DECYCLE": B.F_LITERAL_DECYCLE, "SYNC_INSERT": B.F_SYNC_INSERT}
