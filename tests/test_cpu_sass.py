@@ -1,0 +1,43 @@
+"""Static checks on the sm_100a code of the built library (no GPU needed): the instructions the design relies on are
+really in the hot kernels.  DESIGN.md §4.3: the store kernel fetches a 32-byte slot with ONE 256-bit load and requests
+the next step's home sectors with an L2 prefetch; §4.1: the enumerate kernel keeps its state in registers."""
+import os
+import re
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.join(os.path.dirname(__file__), "..")
+LIB = os.path.join(ROOT, "brisk_b200", "libbrisk_b200.so")
+CUOBJDUMP = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+
+
+def _sass(fun):
+    if not os.path.exists(CUOBJDUMP):
+        pytest.skip("cuobjdump not installed")
+    out = subprocess.run([CUOBJDUMP, "-sass", "-fun", fun, LIB], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-400:]
+    return out.stdout
+
+
+def test_library_is_built_for_sm_100a():
+    if not os.path.exists(CUOBJDUMP):
+        pytest.skip("cuobjdump not installed")
+    out = subprocess.run([CUOBJDUMP, "-lelf", LIB], capture_output=True, text=True, timeout=120).stdout
+    assert "sm_100a" in out, out
+
+
+@pytest.mark.parametrize("mode", [0, 2])  # COUNT, GET at k > 32 (32-byte slots)
+def test_store_kernel_loads_a_slot_with_one_256_bit_request_and_prefetches(mode):
+    sass = _sass("_Z14records_kernelILi4ELi2ELi%dEEv11BriskParamsPKyy9StoreView6OccOut" % mode)
+    assert re.search(r"LDG\.E(\.\w+)*\.256", sass), "no 256-bit load in records_kernel<4,2,%d>" % mode
+    assert "CCTL.E.PF2" in sass, "no L2 prefetch in records_kernel<4,2,%d>" % mode
+    assert "REDUX" in sass, "the lane -> record map is expected to use a warp-wide reduce"
+    assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in the store kernel"
+
+
+def test_enumerate_kernel_keeps_its_state_in_registers():
+    sass = _sass("_Z16enumerate_kernelILi4ELb0EEv11BriskParamsPKyS2_yy7EnumOut")
+    assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in enumerate_kernel<4, ringless>"
+    assert "DFMA" in sass  # the rolled decycling sums are double arithmetic, like DecyclingSet::memDouble
