@@ -24,6 +24,7 @@ NO_SLOT = np.uint64(0xFFFFFFFFFFFFFFFF)
 F_MANAGED = 1
 F_LITERAL_DECYCLE = 2
 F_SYNC_INSERT = 4
+F_GENERIC_ENUM = 8
 
 
 class BriskError(RuntimeError):

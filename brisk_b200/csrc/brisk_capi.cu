@@ -85,13 +85,15 @@ struct brisk_handle {
     u64 *overflow = nullptr;
     uint64_t ovf_cap = 0;
     uint64_t n_keys = 0, n_new_recs = 0;
+    uint64_t pending_incoming = 0, keys_before = 0;  // the insert whose new-key rate settle() will measure
+    double new_rate = 1.0;                           // new keys per incoming occurrence of the last insert
     // scratch
     DevBuf d_bases, d_offsets, d_packed, d_recs, d_rec_occ, d_kmer_base, d_cnt, d_out_slots, d_out_flags, d_out_data,
         d_kmers, d_cub;
     // partition / exchange (sharded index and the partition entry point)
     DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_a, d_fa_b, d_fa_chunks;  // FASTA ingest
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
-    double2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
+    int2 *dec_tab = nullptr;  // grouped decycling weights (BriskParams::dec_tab)
     u64 *d_part2 = nullptr;  // [64] totals, [65] starts, [64] cursors of the table-region partition
     u64 *d_part = nullptr;  // [64] totals, [65] starts, [64] cursors, [64*64] all-gathered totals
     Comm *comm = nullptr;
@@ -149,15 +151,41 @@ static int fill_params(BriskParams &P, int k, int m, int b, uint32_t flags) {
         P.coef[i + 2] = 2 * P.coef[i + 1];
         P.coef[i + 3] = 3 * P.coef[i + 1];
     }
-    for (int q = 0; q < m; q++) {
-        P.tw_c[q] = cos(unit * q);
-        P.tw_s[q] = sin(unit * q);
+    // fixed-point tables of the rolled decycling class (enumerate.cuh) and the band inside which the literal sum
+    // decides.  Error of R, R(rot) in units of 2^-22: table rounding 0.5 per term and component in 2^-24 units, bit
+    // planes of at most m terms, X = A +- 2B -> 1.5 m / 4; the rotation by (cos, sin) multiplies by at most sqrt(2);
+    // rotation constants rounded at 2^-30 (|X| <= 3 m); two truncating high-multiplies: 2.
+    for (int q = 0; q < 32; q++) {
+        const double c = cos(unit * q), sn = sin(unit * q);
+        P.dec_tw[q] = make_int2((int)llround(c * 16777216.0), (int)llround(sn * 16777216.0));
+        P.dec_rot[q] = make_int2((int)llround(c * 1073741824.0), (int)llround(sn * 1073741824.0));
     }
-    P.rot_c = cos(unit); P.rot_s = sin(unit);
-    P.in_c = cos(unit * (m - 1)); P.in_s = sin(unit * (m - 1));
-    P.guard = 1e-9;
+    P.rot1_c30 = P.dec_rot[1].x; P.rot1_s30 = P.dec_rot[1].y;
+    {
+        const double err = 1.5 * m / 4.0 * 1.41422 + 3.0 * m / 256.0 + 2.0;
+        P.dec_th = (int)ceil(P.eps * 4194304.0 + err) + 2;
+    }
     P.polyA_hash = bfc_hash_literal(P.coef, P.eps, 0, P.m_mask, m);
     return BRISK_OK;
+}
+
+// grouped decycling tables (2^24 fixed point): entry (g, v) = sum_j code(nucleotide j of v) * w^(m-1-(3g+j)), positions >= m weigh 0
+static std::vector<int2> decycle_group_table(int m) {
+    const int groups = (m + 2) / 3;
+    const double unit = 2 * M_PI / m;
+    std::vector<int2> tab((size_t)groups * 64);
+    for (int g = 0; g < groups; g++)
+        for (int v = 0; v < 64; v++) {
+            double sr = 0, si = 0;
+            for (int j = 0; j < 3; j++) {
+                const int pos = 3 * g + j, code = (v >> (2 * j)) & 3;
+                if (pos >= m) break;
+                sr += code * cos(unit * (m - 1 - pos));
+                si += code * sin(unit * (m - 1 - pos));
+            }
+            tab[(size_t)g * 64 + v] = make_int2((int)llround(sr * 16777216.0), (int)llround(si * 16777216.0));
+        }
+    return tab;
 }
 
 static StoreView view_of(brisk_handle *h) {
@@ -263,24 +291,12 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
     CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
-    {  // grouped decycling tables: entry (g, v) = sum_j code(nucleotide j of v) * w^(m-1-(3g+j)), positions >= m weigh 0
-        const int groups = (m + 2) / 3;
-        std::vector<double2> tab((size_t)groups * 64);
-        for (int g = 0; g < groups; g++)
-            for (int v = 0; v < 64; v++) {
-                double sr = 0, si = 0;
-                for (int j = 0; j < 3; j++) {
-                    const int pos = 3 * g + j, code = (v >> (2 * j)) & 3;
-                    if (pos >= m) break;
-                    sr += code * h->P.tw_c[m - 1 - pos];
-                    si += code * h->P.tw_s[m - 1 - pos];
-                }
-                tab[(size_t)g * 64 + v] = make_double2(sr, si);
-            }
-        CK(cudaMalloc((void **)&h->dec_tab, tab.size() * sizeof(double2)));
-        CK(cudaMemcpy(h->dec_tab, tab.data(), tab.size() * sizeof(double2), cudaMemcpyHostToDevice));
+    {
+        std::vector<int2> tab = decycle_group_table(m);
+        CK(cudaMalloc((void **)&h->dec_tab, tab.size() * sizeof(int2)));
+        CK(cudaMemcpy(h->dec_tab, tab.data(), tab.size() * sizeof(int2), cudaMemcpyHostToDevice));
         h->P.dec_tab = h->dec_tab;
-        h->P.dec_groups = groups;
+        h->P.dec_groups = (m + 2) / 3;
     }
     CK(cudaMalloc((void **)&h->d_part2, (64 + 65 + 64 + 7) * sizeof(uint64_t)));
     CK(cudaMalloc((void **)&h->d_part, (64 + 65 + 64 + 64 * 64 + 7) * sizeof(uint64_t)));
@@ -349,6 +365,16 @@ struct ReadBatch {
 static int stage_reads(brisk_handle *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, ReadBatch &B) {
     B.n_reads = n_reads;
     uint64_t total = 0;
+    static const uint64_t zero_offsets[1] = {0};
+    if (n_reads == 0) { offsets = zero_offsets; bases = nullptr; }  // a rank of a sharded index may have no reads: (NULL, NULL, 0) is allowed
+    std::vector<uint64_t> h_off_copy;
+    if (n_reads && is_device_ptr(offsets) && !is_device_ptr(bases)) {
+        // bases on the host, offsets on the device: the chunk planner reads the offsets on the host
+        h_off_copy.resize(n_reads + 1);
+        CK(cudaMemcpyAsync(h_off_copy.data(), offsets, (n_reads + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        offsets = h_off_copy.data();
+    }
     if (is_device_ptr(offsets)) {
         CK(cudaMemcpyAsync(&total, offsets + n_reads, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
@@ -420,20 +446,35 @@ static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
     return BRISK_OK;
 }
 
-template <int RW, bool RING>
+template <int KT, int MT, int RW, bool RING, bool LIT>
 static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
-    size_t smem = ((RING ? (size_t)h->P.w * ENUM_THREADS : 0) + ENUM_POOL) * sizeof(u64) + 4 * h->P.m * sizeof(double) +
-                  64 * (size_t)h->P.dec_groups * sizeof(double2);
-    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<RW, RING>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    typedef typename KM<KT, MT>::hash_t hash_t;
+    size_t smem = (RING ? ((size_t)h->P.w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 * 8 : 0) + ENUM_POOL * sizeof(u64) +
+                  4 * h->P.m * sizeof(double) + 64 * (size_t)h->P.dec_groups * sizeof(int2);
+    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<KT, MT, RW, RING, LIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned blocks = (unsigned)((r1 - r0 + ENUM_THREADS - 1) / ENUM_THREADS);
-    enumerate_kernel<RW, RING><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
+    enumerate_kernel<KT, MT, RW, RING, LIT><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
     return cudaGetLastError();
 }
+// generic (k, m): run-time parameters; the literal decycling mode (a debug / verification switch) only exists here
 template <int RW>
-static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
+static cudaError_t launch_enum_generic(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
     // k > 32: most window positions of a rescan are recomputed anyway, so the ring only costs shared memory
-    return h->use_ring ? launch_enum_t<RW, true>(h, B, r0, r1, out) : launch_enum_t<RW, false>(h, B, r0, r1, out);
+    if (h->P.literal_decycle)
+        return h->use_ring ? launch_enum_t<0, 0, RW, true, true>(h, B, r0, r1, out) : launch_enum_t<0, 0, RW, false, true>(h, B, r0, r1, out);
+    return h->use_ring ? launch_enum_t<0, 0, RW, true, false>(h, B, r0, r1, out) : launch_enum_t<0, 0, RW, false, false>(h, B, r0, r1, out);
+}
+static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
+    const int k = h->P.k, m = h->P.m, RW = h->P.rec_words;
+    if (!h->P.literal_decycle && !(h->flags & BRISK_F_GENERIC_ENUM)) {
+        // the parameter sets of BASELINE.json's configurations: k and m compiled in
+        if (k == 63 && m == 21 && RW == 4 && !h->use_ring) return launch_enum_t<63, 21, 4, false, false>(h, B, r0, r1, out);
+        if (k == 64 && m == 23 && RW == 4 && !h->use_ring) return launch_enum_t<64, 23, 4, false, false>(h, B, r0, r1, out);
+        if (k == 31 && m == 15 && RW == 2 && h->use_ring) return launch_enum_t<31, 15, 2, true, false>(h, B, r0, r1, out);
+        if (k == 31 && m == 19 && RW == 2 && h->use_ring) return launch_enum_t<31, 19, 2, true, false>(h, B, r0, r1, out);
+    }
+    return RW == 2 ? launch_enum_generic<2>(h, B, r0, r1, out) : RW == 4 ? launch_enum_generic<4>(h, B, r0, r1, out) : launch_enum_generic<6>(h, B, r0, r1, out);
 }
 
 __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *counts) {
@@ -490,7 +531,7 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
             if (c == 0) CK(cudaEventRecord(h->ev[1], h->stream));
             const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
             if (r1 == r0) continue;
-            cudaError_t e = RW == 2 ? launch_enum<2>(h, B, r0, r1, out) : RW == 4 ? launch_enum<4>(h, B, r0, r1, out) : launch_enum<6>(h, B, r0, r1, out);
+            cudaError_t e = launch_enum(h, B, r0, r1, out);
             CK(e);
             h->last_launches++;
         }
@@ -760,10 +801,28 @@ static int return_results(brisk_handle *h, const Exchange &X, uint64_t n_recs, b
     return BRISK_OK;
 }
 
-// makes room for `incoming` more k-mer occurrences before an insert
+// makes room for `incoming` more k-mer occurrences before an insert.  The number of NEW keys among them is estimated
+// from the capacity hint while it lasts and from the new-key rate of the previous insert once the stored keys approach
+// or pass the hint (a hint that is too small must not stop the table from growing ahead of the batch: with the table
+// nearly full every insert walks to the probe limit and is parked).  The overflow arena is sized with the batch, so
+// that even a badly underestimated batch is parked and replayed, not dropped.
 static int pregrow(brisk_handle *h, uint64_t incoming) {
     uint64_t est_new = incoming;
-    if (h->hint) est_new = std::min<uint64_t>(incoming, h->hint > h->n_keys ? h->hint - h->n_keys : 0);
+    if (h->hint) {
+        const uint64_t by_hint = std::min<uint64_t>(incoming, h->hint > h->n_keys ? h->hint - h->n_keys : 0);
+        const uint64_t by_rate = std::min<uint64_t>(incoming, (uint64_t)((1.5 * h->new_rate + 0.02) * (double)incoming));
+        est_new = std::max(by_hint, by_rate);
+    }
+    h->pending_incoming = incoming;
+    h->keys_before = h->n_keys;
+    const uint64_t want_ovf = std::max<uint64_t>(1u << 20, incoming / 16);
+    if (want_ovf > h->ovf_cap) {
+        if (h->overflow) CK(cudaFree(h->overflow));
+        h->overflow = nullptr;
+        h->ovf_cap = 0;
+        CK(cudaMalloc((void **)&h->overflow, want_ovf * 3 * sizeof(uint64_t)));
+        h->ovf_cap = want_ovf;
+    }
     uint64_t need = h->n_keys + est_new;
     if (need * 10 > h->cap * 7) return grow_to(h, pow2ceil(need * 2));
     return BRISK_OK;
@@ -778,9 +837,19 @@ static int settle(brisk_handle *h) {
         h->n_keys = c[0];
         h->n_new_recs = c[2];
         uint64_t parked = c[1];
+        if (round == 0 && h->pending_incoming) {  // new-key rate of this insert (parked ones count as new), for the next pregrow
+            h->new_rate = std::min(1.0, (double)(h->n_keys - h->keys_before + parked) / (double)h->pending_incoming);
+            h->pending_incoming = 0;
+        }
         if (parked == 0) return BRISK_OK;
-        if (parked > h->ovf_cap) return fail(BRISK_E_FULL, "bucket store overflow: more than 2^20 inserts hit the probe limit; "
-                                                          "give brisk_create a capacity_hint or call brisk_reserve");
+        if (parked > h->ovf_cap) {
+            // the arena holds 1/16 of the batch's occurrences: this takes a table that was nearly full before a batch of
+            // almost only new keys.  The inserts beyond the arena are lost; the handle stays usable.
+            CK(cudaMemsetAsync(h->counters + 1, 0, sizeof(uint64_t), h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+            return fail(BRISK_E_FULL, "bucket store overflow: " + std::to_string(parked - h->ovf_cap) + " inserts of the last batch hit the "
+                                      "probe limit beyond the overflow arena and were dropped; call brisk_reserve ahead of such batches");
+        }
         // move the parked entries aside, grow, replay
         DevBuf tmp;
         CK(tmp.ensure(parked * 3 * sizeof(uint64_t)));
@@ -962,6 +1031,7 @@ extern "C" int brisk_get_reads(brisk_t *h, const char *bases, const uint64_t *of
 extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *recs,
                                      uint64_t cap_recs, uint64_t *n_recs_out, uint32_t *rec_words) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_reads && (!bases || !offsets)) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     SETTLE_PENDING(h);
@@ -992,6 +1062,7 @@ extern "C" int brisk_enumerate_reads(brisk_t *h, const char *bases, const uint64
 extern "C" int brisk_enumerate_reads_tagged(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint64_t *recs,
                                             uint64_t cap_recs, uint64_t *n_recs_out, uint32_t *rec_words, uint64_t *occ) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_reads && (!bases || !offsets)) return fail(BRISK_E_PARAM, "null input");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     SETTLE_PENDING(h);
@@ -1374,6 +1445,7 @@ extern "C" int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
 extern "C" int brisk_partition_reads(brisk_t *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, uint32_t n_ranks,
                                      uint64_t *recs, uint64_t cap_recs, uint64_t *starts, uint32_t *rec_words) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
+    if (n_reads && (!bases || !offsets)) return fail(BRISK_E_PARAM, "null input");
     if (n_ranks == 0 || n_ranks > PART_MAX_RANKS) return fail(BRISK_E_PARAM, "n_ranks must be 1..64");
     if (!starts) return fail(BRISK_E_PARAM, "starts is null");
     std::lock_guard<std::recursive_mutex> lock(h->mu);
@@ -1455,6 +1527,22 @@ extern "C" uint32_t brisk_owner_of_bucket(uint64_t bucket_id, uint8_t b, uint32_
 extern "C" int brisk_exchange_plan(const uint64_t *counts, int n_ranks, int rank, uint64_t *send_start, uint64_t *recv_start) {
     if (!counts || !send_start || !recv_start || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(BRISK_E_PARAM, "bad argument");
     exchange_plan(counts, n_ranks, rank, send_start, recv_start);
+    return BRISK_OK;
+}
+// the fixed-point tables of the rolled decycling class (pure host arithmetic; the CPU tests replay the kernel's formula
+// against DecyclingSet::memDouble with them)
+extern "C" int brisk_decycle_tables(uint8_t k, uint8_t m, uint8_t b, int32_t *tw, int32_t *rot, int32_t *th, int32_t *groups_tab) {
+    BriskParams P;
+    if (fill_params(P, k, m, b, 0) != BRISK_OK) return fail(BRISK_E_PARAM, "bad parameters");
+    for (int q = 0; q < 32; q++) {
+        if (tw) { tw[2 * q] = P.dec_tw[q].x; tw[2 * q + 1] = P.dec_tw[q].y; }
+        if (rot) { rot[2 * q] = P.dec_rot[q].x; rot[2 * q + 1] = P.dec_rot[q].y; }
+    }
+    if (th) *th = P.dec_th;
+    if (groups_tab) {
+        std::vector<int2> tab = decycle_group_table(m);
+        memcpy(groups_tab, tab.data(), tab.size() * sizeof(int2));
+    }
     return BRISK_OK;
 }
 extern "C" int brisk_comm_unique_id(uint8_t id[128]) {

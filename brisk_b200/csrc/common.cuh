@@ -28,15 +28,16 @@ struct BriskParams {
     u64 bucket_mask;   // 4^b - 1
     u64 polyA_hash;    // bfc_hash_64 of the all-A m-mer (zero-padded pseudo m-mers)
     double eps;        // Decycling.h:19
-    double rot_c, rot_s;    // cos, sin of 2*pi/m
-    double in_c, in_s;      // cos, sin of 2*pi*(m-1)/m: weight of the entering base
-    double guard;           // |R -/+ eps| below this -> literal recomputation
     double coef[4 * 32];    // DecyclingSet::coef, computed on the host with the same libm (Decycling.cpp:7-13)
-    double tw_c[32], tw_s[32];  // cos, sin of 2*pi*q/m
-    // [dec_groups][64] complex partial sums of the decycling weights over groups of 3 nucleotides (device memory,
-    // copied to shared memory by the enumeration kernel): entry (g, v) = sum_{j<3} code(nucleotide j of v) *
-    // w^(m-1-(3g+j)), w = exp(2*pi*i/m); built in brisk_create
-    const double2 *dec_tab;
+    // decycling class in fixed point (enumerate.cuh): w = exp(2 pi i / m)
+    int2 dec_tw[32];        // (cos, sin)(2 pi q / m) * 2^24: weight of a base at read position u, q = u mod m
+    int2 dec_rot[32];       // (cos, sin)(2 pi q / m) * 2^30: rotation back to the m-mer's own frame
+    int rot1_c30, rot1_s30; // = dec_rot[1]
+    int dec_th;             // |R|, |R(rot)| (units of 2^-22) at or below this -> literal recomputation
+    // [dec_groups][64] fixed-point (2^24) complex partial sums of the decycling weights over groups of 3 nucleotides
+    // (device memory, copied to shared memory by the enumeration kernel): entry (g, v) = sum_{j<3} code(nucleotide j
+    // of v) * w^(m-1-(3g+j)); built in brisk_create
+    const int2 *dec_tab;
     int dec_groups;  // ceil(m / 3)
 };
 
@@ -130,28 +131,6 @@ __host__ __device__ __forceinline__ u32 dec_mem_double(const double *coef, doubl
 // bfc_hash_64 (brisk/hashing.cpp:8-19), literal
 __host__ __device__ __forceinline__ u64 bfc_hash_literal(const double *coef, double eps, u64 key, u64 mask, int m) {
     return ((u64)dec_mem_double(coef, eps, key, m) << 62) + bfc_mix(key, mask);
-}
-
-// decycling class of an arbitrary m-mer from the grouped tables: S = sum of the group entries, R = Im(S),
-// R(rot) = Im(w S); whenever either value is within `guard` of a threshold the literal
-// summation decides, so the class is always the one DecyclingSet::memDouble returns.
-__device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double *coef, const double2 *tab, u64 seq) {
-    double Sr = 0, Si = 0;
-    // m <= 32: at most 11 groups of 3 nucleotides.  Unrolled with constant table offsets: the loads of all groups
-    // issue back to back (a counted loop serialised them behind its own bookkeeping)
-#pragma unroll
-    for (int g = 0; g < 11; g++) {
-        if (g < P.dec_groups) {
-            const double2 e = tab[g * 64 + (int)((seq >> (6 * g)) & 63)];
-            Sr += e.x;
-            Si += e.y;
-        }
-    }
-    const double R = Si, R2 = fma(Sr, P.rot_s, Si * P.rot_c);
-    if (fabs(fabs(R) - P.eps) < P.guard || fabs(fabs(R2) - P.eps) < P.guard) return dec_mem_double(coef, P.eps, seq, P.m);
-    if (R > P.eps) return R2 < P.eps ? 0u : 2u;
-    if (R < -P.eps) return R2 > -P.eps ? 1u : 2u;
-    return 2u;
 }
 
 // ---------------------------------------------------------------- packed reads

@@ -1,21 +1,26 @@
 // enumerate.cuh — 2-bit packing and superkmer enumeration (north-star items 1-4).
 //
-// pack_reads_kernel     : ASCII -> 2-bit, one warp per read                         (Kmers.cpp:442-444)
-// enumerate_kernel<RW>  : one THREAD per read streams the read once, rolling the forward / reverse
-//                         m-mer, its order hash (hashing.cpp:8-19) and decycling class
-//                         (Decycling.cpp:38-52), and replays SuperKmerEnumerator::next
-//                         (Kmers.cpp:522-603) literally: seed get_minimizer on the (k-1)-mer, strict
-//                         "smaller hash" takeover, full rescan when the minimizer leaves the window,
-//                         the 64-bit truncation of get_minimizer for k > 32 (Q3) and its tie rules (Q5).
-//                         Superkmer descriptors are staged in shared memory and expanded into packed
-//                         records by the whole CTA with coalesced 128-bit stores.
+// pack_reads_kernel        : ASCII -> 2-bit, one warp per read                         (Kmers.cpp:442-444)
+// enumerate_kernel<KT,MT,…>: one THREAD per read (or per segment of a long read, see EnumSeg) streams its bases once,
+//                            rolling the forward / reverse m-mer, its order hash (hashing.cpp:8-19) and decycling
+//                            class (Decycling.cpp:38-52), and replays SuperKmerEnumerator::next (Kmers.cpp:522-603)
+//                            literally: seed get_minimizer on the (k-1)-mer, strict "smaller hash" takeover, full
+//                            rescan when the minimizer leaves the window, the 64-bit truncation of get_minimizer for
+//                            k > 32 (Q3) and its tie rules (Q5).  Rescans are done by the whole warp for one requesting
+//                            lane at a time.  Superkmer descriptors are staged in shared memory and expanded into
+//                            packed records by the whole CTA with coalesced 128-bit stores.
+//
+// KT, MT > 0: k and m are compile-time constants (the five configurations of BASELINE.json); every shift, mask and
+// window length is an immediate, m-mers of m <= 16 live in 32-bit registers, order hashes of m <= 15 too.
+// KT = MT = 0: the same code with k, m read from BriskParams (any other parameter set).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 #define ENUM_THREADS 128
 #define ENUM_POOL 384
 #define ENUM_SYNC_STEPS 32
-#define DEC_RESYNC 128
 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__restrict__ bases,
@@ -47,6 +52,89 @@ __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__
 }
 
 // ---------------------------------------------------------------------------------------------
+// compile-time / run-time view of (k, m)
+template <int KT, int MT>
+struct KM {
+    typedef typename std::conditional<(MT > 0 && MT <= 16), u32, u64>::type mer_t;    // an m-mer
+    typedef typename std::conditional<(MT > 0 && MT <= 15), u32, u64>::type hash_t;   // class bits + mix of an m-mer
+    static constexpr bool HASH32 = (MT > 0 && MT <= 15);
+    __device__ __forceinline__ static int k(const BriskParams &P) { return KT ? KT : P.k; }
+    __device__ __forceinline__ static int m(const BriskParams &P) { return MT ? MT : P.m; }
+    __device__ __forceinline__ static mer_t m_mask(const BriskParams &P) {
+        return MT ? (mer_t)((MT >= 32) ? ~0ull : ((1ull << (2 * (MT & 31))) - 1)) : (mer_t)P.m_mask;
+    }
+    __device__ __forceinline__ static int s(const BriskParams &P) { return P.s; }
+    // order hash = (class << 62) + mix (hashing.cpp:18); in 32 bits the class sits right above the 2m <= 30 mix bits
+    __device__ __forceinline__ static hash_t make_hash(u32 cls, mer_t mix) {
+        if (HASH32) return (hash_t)((cls << 30) | (u32)mix);
+        return (hash_t)(((u64)cls << 62) + (u64)mix);
+    }
+    __device__ __forceinline__ static mer_t mix(mer_t key, mer_t mask) {
+        if (sizeof(mer_t) == 4) return (mer_t)bfc_mix32((u32)key, (u32)mask);
+        return (mer_t)bfc_mix((u64)key, (u64)mask);
+    }
+    // rcbc (brisk/Kmers.cpp:320-332) on an m-mer
+    __device__ __forceinline__ static mer_t rc(mer_t v, int m) {
+        if (sizeof(mer_t) == 4) {
+            u32 x = __brev((u32)v ^ 0xaaaaaaaau);
+            x = ((x & 0x55555555u) << 1) | ((x >> 1) & 0x55555555u);
+            return (mer_t)(x >> (32 - 2 * m));
+        }
+        return (mer_t)rcbc((u64)v, m);
+    }
+};
+
+// minimum over the warp
+__device__ __forceinline__ u64 warp_min(u64 v) {
+    u32 hi = (u32)(v >> 32), lo = (u32)v;
+    u32 mhi = __reduce_min_sync(0xffffffffu, hi);
+    u32 mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    return ((u64)mhi << 32) | mlo;
+}
+__device__ __forceinline__ u32 warp_min(u32 v) { return __reduce_min_sync(0xffffffffu, v); }
+
+// ---- decycling class in fixed point -------------------------------------------------------------
+// DecyclingSet::memDouble (Decycling.cpp:38-52) classifies an m-mer by R = Im(S) and R(rot) = Im(w S),
+// S = sum_j code_j w^j over the LEFT positions j of the m-mer, w = exp(2 pi i / m), against +-1e-6.
+// Rolled: a base at read position u weighs w^(u mod m) (exact integer table, 2^24 fixed point), so the window sum
+// T = sum_u code_u w^(u mod m) rolls with one table entry per step and never drifts; S = w^(-p) T for the m-mer
+// starting at p.  The two code bit planes are kept apart (code = a + 2b) because the reverse strand's sum is
+// w^(-1) conj(A - 2B).  Whenever |R| or |R(rot)| is inside the threshold band (eps + the worst-case fixed-point
+// error, P.dec_th) the literal double summation decides: the class is always the reference's.
+struct DecRot { int c30, s30; };
+__device__ __forceinline__ int dec_im(int Xr, int Xi, int c30, int s30) { return __mulhi(Xi, c30) - __mulhi(Xr, s30); }
+
+// class from the two bit-plane sums; rot_p / rot_q: cos, sin (2^30) of 2 pi p / m and 2 pi (p - 1) / m, p = start of the m-mer
+__device__ __forceinline__ u32 dec_class_rolled(int Ar, int Ai, int Br, int Bi, bool rv, int pc, int ps, int qc, int qs, int th,
+                                                bool &ambiguous) {
+    const int Xr = rv ? Ar - 2 * Br : Ar + 2 * Br, Xi = rv ? Ai - 2 * Bi : Ai + 2 * Bi;
+    const int D0 = dec_im(Xr, Xi, pc, ps);  // Im(w^-p X)
+    const int D1 = dec_im(Xr, Xi, qc, qs);  // Im(w^(1-p) X)
+    const int R = rv ? -D1 : D0, R2 = rv ? -D0 : D1;
+    ambiguous = min(abs(R), abs(R2)) <= th;
+    return R > 0 ? (R2 < 0 ? 0u : 2u) : (R2 > 0 ? 1u : 2u);
+}
+
+// class of an arbitrary m-mer from the grouped tables: tab[g][v] = fixed-point sum of code * w^(left position) over the
+// three nucleotides 3g .. 3g+2 (from the right end) of the m-mer
+template <int MT>
+__device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double *coef, const int2 *tab, u64 seq, int m) {
+    int Sr = 0, Si = 0;
+    constexpr int G = MT ? (MT + 2) / 3 : 11;
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        if (MT || g < P.dec_groups) {
+            const int2 e = tab[g * 64 + (int)((seq >> (6 * g)) & 63)];
+            Sr += e.x;
+            Si += e.y;
+        }
+    }
+    const int R = Si >> 2, R2 = __mulhi(Sr, P.rot1_s30) + __mulhi(Si, P.rot1_c30);
+    if (min(abs(R), abs(R2)) <= P.dec_th) return dec_mem_double(coef, P.eps, seq, m);
+    return R > 0 ? (R2 < 0 ? 0u : 2u) : (R2 > 0 ? 1u : 2u);
+}
+
+// ---------------------------------------------------------------------------------------------
 // superkmer descriptor staged in shared memory
 __device__ __forceinline__ u64 make_desc(u32 i0, int n, int pos0, bool rev, int tid) {
     return (u64)i0 | ((u64)n << 32) | ((u64)pos0 << 40) | ((u64)rev << 48) | ((u64)tid << 49);
@@ -55,18 +143,20 @@ __device__ __forceinline__ u64 make_desc(u32 i0, int n, int pos0, bool rev, int 
 // Builds the packed record of one superkmer: k-mers i0 .. i0+n-1 of the read (read order), whose first
 // k-mer had mini_pos = pos0, minimizer on the reverse strand when rev.  Emission order and minimizer_idx
 // follow Kmers.cpp:578-584 and the vector reversal at :554-556/:567-569/:597-599.
-template <int RW>
-__device__ __forceinline__ void build_record(const BriskParams &P, const u64 *pk, u32 i0, int n, int pos0, bool rev,
+template <int KT, int MT, int RW>
+__device__ __forceinline__ void build_record(const BriskParams &P, const u64 *pk, u64 i0, int n, int pos0, bool rev,
                                              u64 (&rec)[RW]) {
-    const int len = n + P.k - 1;
+    const int k = KM<KT, MT>::k(P), m = KM<KT, MT>::m(P);
+    const u64 m_mask = (u64)KM<KT, MT>::m_mask(P);
+    const int len = n + k - 1;
     // bases [i0, i0+len) right-aligned in rec[]
 #pragma unroll
     for (int wi = 0; wi < RW; wi++) {
         int endb = len - 32 * wi;  // bases [endb-32, endb) of the segment go to word wi
         u64 x = 0;
         if (endb > 0) {
-            if (endb >= 32) x = get_bits64(pk, (u64)i0 + endb - 32);
-            else x = get_bits64(pk, (u64)i0) >> (64 - 2 * endb);
+            if (endb >= 32) x = get_bits64(pk, i0 + endb - 32);
+            else x = get_bits64(pk, i0) >> (64 - 2 * endb);
         }
         rec[wi] = x;
     }
@@ -80,11 +170,11 @@ __device__ __forceinline__ void build_record(const BriskParams &P, const u64 *pk
 #pragma unroll
         for (int wi = 0; wi < RW; wi++) rec[wi] = t[wi];
         mw_shr<RW, 7>(rec, 64 * RW - 2 * len);
-        idx0 = P.k - P.m - pos0 - n + 1;
+        idx0 = k - m - pos0 - n + 1;
     }
     // minimizer slice of the first emitted k-mer: nucleotides [idx0, idx0+m) from its right end
-    u64 W = mw_extract64<RW, 3>(rec, 2 * (n - 1 + idx0)) & P.m_mask;
-    u64 bucket = (bfc_mix(W, P.m_mask) >> (2 * P.s)) & P.bucket_mask;
+    u64 W = mw_extract64<RW, 3>(rec, 2 * (n - 1 + idx0)) & m_mask;
+    u64 bucket = (bfc_mix(W, m_mask) >> (2 * P.s)) & P.bucket_mask;
     rec[RW - 1] |= rec_header(P, bucket, n, idx0);
 }
 
@@ -103,31 +193,49 @@ struct EnumOut {
     const u64 *kmer_base;  // optional [n_reads]: occurrence index of k-mer 0 of each read
 };
 
-// 64-bit minimum over the warp
-__device__ __forceinline__ u64 warp_min64(u64 v) {
-    u32 hi = (u32)(v >> 32), lo = (u32)v;
-    u32 mhi = __reduce_min_sync(0xffffffffu, hi);
-    u32 mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
-    return ((u64)mhi << 32) | mlo;
-}
+// A long read is cut into segments of k-mers that are enumerated by different threads.  Segment s of a
+// read covers the k-mers [kmer0, kmer1); the thread starts rolling `warm` k-mers earlier with a full rescan
+// (get_minimizer on the k-mer, which is the state the reference has right after an "outdated" event) unless kmer0 = 0
+// (the reference's own seed on the (k-1)-mer), or from the exact state in `st` when one is given (pass 2).
+struct EnumSeg {
+    u64 read;       // index of the read in the batch
+    u64 kmer0;      // first k-mer whose superkmer starts belong to this segment
+    u64 kmer1;      // one past the last
+    u64 start;      // k-mer at which the state machine starts (<= kmer0)
+};
+struct EnumSegState {  // state of the machine right after k-mer `kmer1 - 1` (pass 1 output) / right before `kmer0` (pass 2 input)
+    u64 H;
+    int pos;
+    int rev;
+    u64 i0;    // first k-mer of the open superkmer
+    int pos0;
+    int pad;
+};
 
 // ring of order hashes: slot-major, the column is XOR-swizzled with the slot so that a thread writing its own
 // column and a warp reading one thread's column across slots are both free of bank conflicts
 __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_THREADS + (tid ^ (slot & 31)); }
 
 // RING = true : every thread keeps the order hashes of its last w m-mers in a shared-memory ring; a rescan reads them.
-// RING = false: no ring (shared memory: staging pool + tables only, twice the resident warps at k = 63); a rescan
-//               recomputes the hash of every window position from the requester's last 32 bases, which k > 32 has to
-//               do anyway for most positions (the 64-bit truncation of get_minimizer, Q3).
-template <int RW, bool RING>
+// RING = false: no ring (shared memory: staging pool + tables only); a rescan recomputes the hash of every window
+//               position from the requester's last 32 bases, which k > 32 has to do anyway for most positions (the
+//               64-bit truncation of get_minimizer, Q3); no order hash is computed before the first k-mer is complete.
+// LIT  = true : DecyclingSet::memDouble evaluated literally for every m-mer (BRISK_F_LITERAL_DECYCLE).
+template <int KT, int MT, int RW, bool RING, bool LIT>
 __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 read0, u64 n_reads,
                                                                  EnumOut out) {
+    typedef KM<KT, MT> C;
+    typedef typename C::mer_t mer_t;
+    typedef typename C::hash_t hash_t;
     extern __shared__ u64 smem[];
-    u64 *ring = smem;                                  // [w][ENUM_THREADS] order hashes of the last w m-mers (RING only)
-    u64 *pool = ring + (RING ? (size_t)P.w * ENUM_THREADS : 0);  // [ENUM_POOL] superkmer descriptors
+    const int k = C::k(P), m = C::m(P);
+    const int w = k - m + 1;
+    const mer_t m_mask = C::m_mask(P);
+    hash_t *ring = reinterpret_cast<hash_t *>(smem);   // [w][ENUM_THREADS] order hashes of the last w m-mers (RING only)
+    u64 *pool = smem + (RING ? ((size_t)w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 : 0);  // [ENUM_POOL] superkmer descriptors
     double *coef = (double *)(pool + ENUM_POOL);       // [4m]
-    double2 *dtab = (double2 *)(coef + 4 * P.m);  // [dec_groups][64] grouped decycling weights (16-byte aligned: 4m doubles)
+    int2 *dtab = (int2 *)(coef + 4 * m);               // [dec_groups][64] grouped decycling weights
     __shared__ u32 pool_n;
     __shared__ u32 s_maxL;
     __shared__ u64 s_base;
@@ -136,7 +244,6 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    const int k = P.k, m = P.m;
     const u64 rid = read0 + (u64)blockIdx.x * ENUM_THREADS + tid;  // this launch covers reads [read0, n_reads) of the batch
     u32 L = 0;
     u64 wstart = 0;
@@ -144,7 +251,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
         u64 beg = offsets[rid], end = offsets[rid + 1];
         u64 len = end - beg;
         wstart = packed_start(beg, rid);
-        L = len >= (u64)k ? (u32)len : 0u;  // apps/counter.cpp:233
+        L = (len >= (u64)k && len <= 0xffffffffull) ? (u32)len : 0u;  // apps/counter.cpp:233
     }
     const u64 *pk = packed + wstart;
     rd_start[tid] = wstart;
@@ -158,15 +265,18 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     const u32 maxL = s_maxL;
 
     // rolling state
-    u64 f = 0, r = 0, word = 0, revbits = 0, hist = 0;  // hist: the last 32 bases (RING = false)
-    double Ar = 0, Ai = 0, Br = 0, Bi = 0;
+    mer_t f = 0, r = 0;
+    u64 word = 0, revbits = 0, hist = 0;  // hist: the last 32 bases (RING = false)
+    int Ar = 0, Ai = 0, Br = 0, Bi = 0;   // bit-plane sums of the window, absolute phase (fixed point)
     int rslot = -1;           // ring slot of the newest m-mer (the same for every thread: all reads start at t = 0)
-    u64 H = 0;                // mini_hash
+    int q = 0;                // t mod m (the same for every thread)
+    hash_t H = 0;             // mini_hash
     int pos = 0;              // mini_pos
     bool rev = false;         // reversed
     u32 i0 = 0;               // first k-mer of the open superkmer
     int pos0 = 0;             // mini_pos of that k-mer
     const int rshift = 2 * m - 2;
+    const hash_t polyA = C::make_hash((u32)(P.polyA_hash >> 62), (mer_t)(P.polyA_hash & (u64)m_mask));
 
     auto append = [&](u32 a, int n, int p0, bool rv) {
         u32 slot = atomicAdd(&pool_n, 1u);
@@ -176,149 +286,172 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
             u64 g = atomicAdd(out.rec_count, 1ull);
             if (out.recs && g < out.rec_cap) {
                 u64 rec[RW];
-                build_record<RW>(P, pk, a, n, p0, rv, rec);
+                build_record<KT, MT, RW>(P, pk, a, n, p0, rv, rec);
                 store_record<RW>(out.recs, g, rec);
                 if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rid] + a) << 1) | (u64)rv;
             }
         }
     };
 
+    // one base: forward / reverse m-mer, last 32 bases, bit-plane sums
+    auto roll = [&]() {
+        const u32 code = (u32)(word >> 62);
+        word <<= 2;
+        const u32 leave = (u32)(f >> rshift) & 3u;
+        f = (mer_t)(((f << 2) | code) & m_mask);
+        r = (mer_t)((r >> 2) | ((mer_t)(code ^ 2u) << rshift));
+        if (!RING) hist = (hist << 2) | code;
+        if (!LIT) {
+            const int da = (int)(code & 1u) - (int)(leave & 1u), db = (int)(code >> 1) - (int)(leave >> 1);
+            const int tc = P.dec_tw[q].x, ts = P.dec_tw[q].y;
+            Ar += da * tc; Ai += da * ts;
+            Br += db * tc; Bi += db * ts;
+        }
+    };
+    // order hash of the newest m-mer (hashing.cpp:8-19); rv = it is the reverse strand that is canonical
+    auto order_hash = [&](bool &rv) -> hash_t {
+        rv = r < f;
+        const mer_t canon = rv ? r : f;
+        u32 cls;
+        if (LIT) {
+            cls = dec_mem_double(coef, P.eps, (u64)canon, m);
+        } else {
+            // the m-mer ending at base t starts at phase p = (t + 1) mod m = q + 1
+            const int p = q + 1 == m ? 0 : q + 1;
+            bool amb;
+            cls = dec_class_rolled(Ar, Ai, Br, Bi, rv, P.dec_rot[p].x, P.dec_rot[p].y, P.dec_rot[q].x, P.dec_rot[q].y, P.dec_th, amb);
+            if (amb) cls = dec_mem_double(coef, P.eps, (u64)canon, m);
+        }
+        return C::make_hash(cls, C::mix(canon, m_mask));
+    };
+    // get_minimizer (Kmers.cpp:367-408) on the kk-mer ending at base t for the lanes that asked, one requester at a
+    // time, the warp's lanes taking one window position each
+    auto rescans = [&](unsigned req, const int kk, const u32 t) {
+        const int nmax = kk - m;
+        const int real_max = kk > 32 ? 32 - m : nmax;
+        const bool has_hi = nmax >= 32;  // positions >= 32 hold the all-A pseudo m-mer (Q3)
+        u64 cur64 = 0;
+        if (!RING) cur64 = hist;
+        else if (kk > 32 && ((req >> lane) & 1u)) cur64 = get_bits64(pk, (u64)t - 31);
+        while (req) {
+            const int src = __ffs(req) - 1;
+            req &= req - 1;
+            const u64 s_cur = (!RING || kk > 32) ? __shfl_sync(0xffffffffu, cur64, src) : 0ull;
+            const u64 s_revbits = RING ? __shfl_sync(0xffffffffu, revbits, src) : 0ull;
+            const int s_tid = (tid & ~31) | src;
+            hash_t nh = (hash_t)~(hash_t)0;
+            bool prv = false;
+            if (lane <= nmax) {
+                if (RING && lane <= real_max) {
+                    int sl = rslot - lane;
+                    if (sl < 0) sl += w;
+                    nh = ring[ring_at(sl, s_tid)];
+                    prv = (s_revbits >> lane) & 1;
+                } else {
+                    // real m-mer (masked) or the zero-padded top of the truncated k-mer (the mask is a no-op)
+                    const mer_t v = (mer_t)((s_cur >> (2 * lane)) & (u64)m_mask);
+                    const mer_t rc = C::rc(v, m);
+                    const mer_t c = v < rc ? v : rc;
+                    const u32 pc = LIT ? dec_mem_double(coef, P.eps, (u64)c, m) : dec_class_tab<MT>(P, coef, dtab, (u64)c, m);
+                    nh = C::make_hash(pc, C::mix(c, m_mask));
+                    prv = c != v;
+                }
+            }
+            hash_t hm = warp_min(nh);
+            if (has_hi && polyA < hm) hm = polyA;
+            u64 tmask = __ballot_sync(0xffffffffu, nh == hm);
+            if (has_hi && polyA == hm) tmask |= ((((u64)1) << (nmax - 31)) - 1) << 32;
+            const unsigned rvlo = __ballot_sync(0xffffffffu, prv);
+            int mp = __ffsll((long long)tmask) - 1;
+            bool rv0 = mp < 32 ? (rvlo >> mp) & 1u : false;
+            u64 rest = tmask & (tmask - 1);
+            if (rest) {  // equal hashes in the window: the tie rules of Kmers.cpp:389-404, in scan order
+                int cs = 0;
+                if (lane == src) {
+                    int nlo = kk < 32 ? kk : 32;
+                    u64 lo = get_bases(pk, (u64)t + 1 - nlo, nlo);
+                    u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
+                    cs = canonized128(lo, hi, kk) ? 1 : 0;
+                }
+                cs = __shfl_sync(0xffffffffu, cs, src);
+                while (rest) {
+                    const int i2 = __ffsll((long long)rest) - 1;
+                    rest &= rest - 1;
+                    const bool rvi = i2 < 32 ? (rvlo >> i2) & 1u : false;
+                    if (nmax - i2 < mp) { mp = nmax - i2; rv0 = rvi; }
+                    else if (nmax - i2 == mp) { if (!cs) rv0 = false; }
+                }
+            }
+            if (lane == src) { H = hm; pos = mp; rev = rv0; }
+        }
+    };
+    auto next_q = [&]() { q = q + 1 == m ? 0 : q + 1; };
+
     static_assert(ENUM_SYNC_STEPS == 32, "one packed word per block of steps");
+    // phases of a read (t = index of the base being consumed; the same t in every thread):
+    //   t <  e_roll          : the window fills (RING: until the first m-mer is complete; else: until the seed step)
+    //   e_roll <= t < k - 2  : RING only: order hashes go to the ring
+    //   t == k - 2           : seed get_minimizer on the (k-1)-mer (Kmers.cpp:533)
+    //   t >= k - 1           : one k-mer per step
+    const u32 e_roll = RING ? (u32)(m - 1) : (u32)(k - 2);
     for (u32 t0 = 0; t0 < maxL; t0 += ENUM_SYNC_STEPS) {
         if (t0 < L) word = __ldg(pk + (t0 >> 5));  // the 32 bases of this block of steps
-        for (u32 t = t0; t < t0 + ENUM_SYNC_STEPS; t++) {
-            const bool active = t < L;
-            u64 h = 0;
-            bool rv = false;
-            int need_kk = 0;  // k-1: seed get_minimizer (Kmers.cpp:533), k: the minimizer left the window (:551-562)
-            const bool old_rev = rev;
-            if (RING && t + 1 >= (u32)m) rslot = rslot + 1 == P.w ? 0 : rslot + 1;  // same t in every thread: uniform
-            if (active) {
-                const u32 code = (u32)(word >> 62);
-                word <<= 2;
-                const u32 leave = (u32)(f >> rshift) & 3u;
-                f = ((f << 2) | code) & P.m_mask;
-                r = (r >> 2) | ((u64)(code ^ 2u) << rshift);
-                if (!RING) hist = (hist << 2) | code;
-                if (!P.literal_decycle) {
-                    // A = sum of low code bits * w^q, B = sum of high code bits * w^q over the window
-                    double la = (double)(leave & 1u), lb = (double)(leave >> 1);
-                    double ea = (double)(code & 1u), eb = (double)(code >> 1);
-                    double ar = Ar - la, br = Br - lb;
-                    double nAr = fma(Ai, P.rot_s, ar * P.rot_c), nAi = fma(-ar, P.rot_s, Ai * P.rot_c);
-                    double nBr = fma(Bi, P.rot_s, br * P.rot_c), nBi = fma(-br, P.rot_s, Bi * P.rot_c);
-                    Ar = fma(ea, P.in_c, nAr); Ai = fma(ea, P.in_s, nAi);
-                    Br = fma(eb, P.in_c, nBr); Bi = fma(eb, P.in_s, nBi);
-                    if ((t & (DEC_RESYNC - 1)) == DEC_RESYNC - 1) {
-                        // bound the rounding drift on long reads: recompute the sums from the window
-                        double sAr = 0, sAi = 0, sBr = 0, sBi = 0;
-                        for (int q = 0; q < m; q++) {
-                            u32 c = (u32)(f >> (2 * (m - 1 - q))) & 3u;
-                            double tc = P.tw_c[q], ts = P.tw_s[q];
-                            if (c & 1u) { sAr += tc; sAi += ts; }
-                            if (c & 2u) { sBr += tc; sBi += ts; }
-                        }
-                        Ar = sAr; Ai = sAi; Br = sBr; Bi = sBi;
-                    }
+        const u32 t1 = t0 + ENUM_SYNC_STEPS;
+        u32 t = t0;
+        for (; t < t1 && t < e_roll; t++) {
+            if (L) roll();
+            next_q();
+        }
+        if (RING) {
+            for (; t < t1 && t + 2 < (u32)k; t++) {
+                rslot = rslot + 1 == w ? 0 : rslot + 1;
+                if (L) {
+                    roll();
+                    bool rv;
+                    ring[ring_at(rslot, tid)] = order_hash(rv);
+                    revbits = (revbits << 1) | (u64)rv;
                 }
-                if (t + 1 >= (u32)m) {
-                    rv = r < f;
-                    const u64 canon = rv ? r : f;
-                    u32 cls;
-                    if (P.literal_decycle) {
-                        cls = dec_mem_double(coef, P.eps, canon, m);
-                    } else {
-                        // R = Im(S), R(rot) = Im(w S) for the canonical strand (decycling)
-                        double z = rv ? -2.0 : 2.0;
-                        double Xr = fma(z, Br, Ar), Xi = fma(z, Bi, Ai);
-                        double T = fma(Xr, P.rot_s, Xi * P.rot_c);
-                        double R = rv ? -T : Xi, R2 = rv ? -Xi : T;
-                        cls = 2;
-                        if (R > P.eps) { if (R2 < P.eps) cls = 0; }
-                        else if (R < -P.eps) { if (R2 > -P.eps) cls = 1; }
-                        if (fabs(fabs(R) - P.eps) < P.guard || fabs(fabs(R2) - P.eps) < P.guard)
-                            cls = dec_mem_double(coef, P.eps, canon, m);
-                    }
-                    h = ((u64)cls << 62) + bfc_mix(canon, P.m_mask);
-                    if (RING) {
-                        ring[ring_at(rslot, tid)] = h;
-                        revbits = (revbits << 1) | (u64)rv;
-                    }
-                    if (t + 2 == (u32)k) {
-                        need_kk = k - 1;
-                    } else if (t + 1 >= (u32)k) {
-                        pos += 1;
-                        if (pos > k - m) need_kk = k;
-                    }
+                next_q();
+            }
+        }
+        if (t < t1 && t + 2 == (u32)k) {
+            if (RING && t + 1 >= (u32)m) rslot = rslot + 1 == w ? 0 : rslot + 1;
+            if (L) {
+                roll();
+                if (RING && t + 1 >= (u32)m) {
+                    bool rv;
+                    ring[ring_at(rslot, tid)] = order_hash(rv);
+                    revbits = (revbits << 1) | (u64)rv;
                 }
             }
             __syncwarp();
-            // get_minimizer (Kmers.cpp:367-408) for the threads that asked, one requester at a time, the warp's
-            // lanes taking one window position each
-            unsigned req = __ballot_sync(0xffffffffu, need_kk != 0);
-            if (req) {
-                const int kk = (t + 2 == (u32)k) ? k - 1 : k;
-                const int nmax = kk - m;
-                const int real_max = kk > 32 ? 32 - m : nmax;
-                const bool has_hi = nmax >= 32;  // positions >= 32 hold the all-A pseudo m-mer (Q3)
-                u64 cur64 = 0;
-                if (!RING) cur64 = hist;
-                else if (need_kk && kk > 32) cur64 = get_bits64(pk, (u64)t - 31);
-                while (req) {
-                    const int src = __ffs(req) - 1;
-                    req &= req - 1;
-                    const u64 s_cur = __shfl_sync(0xffffffffu, cur64, src);
-                    const u64 s_revbits = __shfl_sync(0xffffffffu, revbits, src);
-                    const int s_tid = (tid & ~31) | src;
-                    u64 nh = ~0ull;
-                    bool prv = false;
-                    if (lane <= nmax) {
-                        if (RING && lane <= real_max) {
-                            int sl = rslot - lane;
-                            if (sl < 0) sl += P.w;
-                            nh = ring[ring_at(sl, s_tid)];
-                            prv = (s_revbits >> lane) & 1;
-                        } else {
-                            // real m-mer (masked) or the zero-padded top of the truncated k-mer (the mask is a no-op)
-                            u64 v = (s_cur >> (2 * lane)) & P.m_mask;
-                            u64 rc = rcbc(v, m);
-                            u64 c = v < rc ? v : rc;
-                            const u32 pc = P.literal_decycle ? dec_mem_double(coef, P.eps, c, m) : dec_class_tab(P, coef, dtab, c);
-                            nh = ((u64)pc << 62) + bfc_mix(c, P.m_mask);
-                            prv = c != v;
-                        }
-                    }
-                    u64 hm = warp_min64(nh);
-                    if (has_hi && P.polyA_hash < hm) hm = P.polyA_hash;
-                    u64 tmask = __ballot_sync(0xffffffffu, nh == hm);
-                    if (has_hi && P.polyA_hash == hm) tmask |= ((((u64)1) << (nmax - 31)) - 1) << 32;
-                    const unsigned rvlo = __ballot_sync(0xffffffffu, prv);
-                    int mp = __ffsll((long long)tmask) - 1;
-                    bool rv0 = mp < 32 ? (rvlo >> mp) & 1u : false;
-                    u64 rest = tmask & (tmask - 1);
-                    if (rest) {  // equal hashes in the window: the tie rules of Kmers.cpp:389-404, in scan order
-                        int cs = 0;
-                        if (lane == src) {
-                            int nlo = kk < 32 ? kk : 32;
-                            u64 lo = get_bases(pk, (u64)t + 1 - nlo, nlo);
-                            u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
-                            cs = canonized128(lo, hi, kk) ? 1 : 0;
-                        }
-                        cs = __shfl_sync(0xffffffffu, cs, src);
-                        while (rest) {
-                            const int i2 = __ffsll((long long)rest) - 1;
-                            rest &= rest - 1;
-                            const bool rvi = i2 < 32 ? (rvlo >> i2) & 1u : false;
-                            if (nmax - i2 < mp) { mp = nmax - i2; rv0 = rvi; }
-                            else if (nmax - i2 == mp) { if (!cs) rv0 = false; }
-                        }
-                    }
-                    if (lane == src) { H = hm; pos = mp; rev = rv0; }
+            const unsigned req = __ballot_sync(0xffffffffu, L != 0);
+            if (req) rescans(req, k - 1, t);
+            next_q();
+            t++;
+        }
+        for (; t < t1; t++) {
+            const bool active = t < L;
+            hash_t h = 0;
+            bool rv = false, need = false;
+            const bool old_rev = rev;
+            if (RING) rslot = rslot + 1 == w ? 0 : rslot + 1;
+            if (active) {
+                roll();
+                h = order_hash(rv);
+                if (RING) {
+                    ring[ring_at(rslot, tid)] = h;
+                    revbits = (revbits << 1) | (u64)rv;
                 }
+                pos += 1;
+                need = pos > k - m;  // the minimizer left the window (Kmers.cpp:551-562)
             }
-            if (active && t + 1 >= (u32)k) {
+            __syncwarp();
+            const unsigned req = __ballot_sync(0xffffffffu, need);
+            if (req) rescans(req, k, t);
+            if (active) {
                 const u32 i = t + 1 - k;
-                bool boundary = need_kk != 0;
+                bool boundary = need;
                 if (!boundary && h < H) {
                     boundary = true;
                     H = h; pos = 0; rev = rv;
@@ -331,6 +464,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                 }
                 if (t + 1 == L) append(i0, (int)(i + 1 - i0), pos0, rev);
             }
+            next_q();
         }
         __syncthreads();
         const u32 cnt_raw = pool_n;
@@ -349,7 +483,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                     int owner = (int)(d >> 49) & 127;
                     bool rvd = (d >> 48) & 1;
                     u64 rec[RW];
-                    build_record<RW>(P, packed + rd_start[owner], (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd, rec);
+                    build_record<KT, MT, RW>(P, packed + rd_start[owner], (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd, rec);
                     store_record<RW>(out.recs, g, rec);
                     if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rd_id[owner]] + (u32)d) << 1) | (u64)rvd;
                 }

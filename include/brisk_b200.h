@@ -50,6 +50,9 @@ typedef struct brisk_handle brisk_t;
                                     * stream order before any later call on the handle reads the store, and a store-full
                                     * error of such a call is reported by the next call or by brisk_sync) */
 
+#define BRISK_F_GENERIC_ENUM 8u     /* debug: enumerate with the run-time-(k, m) kernel even when a compiled-in
+                                    * specialisation exists for the parameter set */
+
 /* one k-mer as the reference's kmer_full carries it */
 typedef struct {
     uint64_t lo, hi;       /* kmer_s */
@@ -172,6 +175,11 @@ uint32_t brisk_owner_of_bucket(uint64_t bucket_id, uint8_t b, uint32_t n_ranks);
 /* send / receive offsets of one exchange from the n x n matrix of record counts (row = sender); both outputs have
  * n_ranks + 1 entries.  Pure host arithmetic. */
 int brisk_exchange_plan(const uint64_t *counts, int n_ranks, int rank, uint64_t *send_start, uint64_t *recv_start);
+
+/* fixed-point tables of the rolled decycling class (pure host arithmetic, no device needed):
+ * tw[64] / rot[64] = (cos, sin)(2 pi q / m) scaled by 2^24 / 2^30 for q < 32, *th = the band (units of 2^-22) inside
+ * which the literal DecyclingSet::memDouble decides, groups_tab[ceil(m/3) * 64 * 2] = the 3-nucleotide partial sums. */
+int brisk_decycle_tables(uint8_t k, uint8_t m, uint8_t b, int32_t *tw, int32_t *rot, int32_t *th, int32_t *groups_tab);
 
 const char *brisk_last_error(void);
 const char *brisk_version(void);

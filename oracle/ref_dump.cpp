@@ -16,8 +16,9 @@
 //   ref_dump count reads.txt k m b out.bin     count like apps/counter.cpp, dump the index
 //   ref_dump query reads.txt k m b out.bin q.txt   count reads.txt, then query q.txt
 //   ref_dump time  reads.txt k m b threads [max_reads]   timed count (hot path only)
-//   ref_dump steps reads.txt k m b threads reads_per_step n_steps
-//                  step j = count chunk j (count_sequence) then query chunk j-1 (query_sequence), timed
+//   ref_dump steps reads.txt k m b threads reads_per_step n_steps [dump.bin|- [decoy.txt]]
+//                  step j = count chunk j (count_sequence) then query chunk j-1 (query_sequence), timed;
+//                  then (threads = 1) the sorted dump of the final index and the aggregate answer to a decoy query
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -263,6 +264,53 @@ int main(int argc, char **argv) {
             fflush(stdout);
         }
         print_stats(index);
+        // optional: sorted dump of the final index (argv[9]) and the aggregate answer to a decoy query file (argv[10]);
+        // both only make sense with threads = 1
+        if (argc > 9 && strcmp(argv[9], "-") != 0) {
+            vector<DumpRec> recs;
+            kmer_full km(0, 0, m, params.dede);
+            index.restart_kmer_enumeration();
+            while (index.next(km)) {
+                DumpRec rec;
+                rec.lo = (uint64_t)km.kmer_s;
+                rec.hi = (uint64_t)(km.kmer_s >> 64);
+                rec.idx = km.minimizer_idx;
+                uint8_t *c = index.get(km);
+                rec.count = c ? *c : 0;
+                if (!c) printf("MISSING_DATA\n");
+                recs.push_back(rec);
+                km.kmer_s = 0;
+            }
+            sort(recs.begin(), recs.end(), [](const DumpRec &a, const DumpRec &b) {
+                if (a.hi != b.hi) return a.hi < b.hi;
+                if (a.lo != b.lo) return a.lo < b.lo;
+                return a.idx < b.idx;
+            });
+            FILE *out = fopen(argv[9], "wb");
+            fwrite(recs.data(), sizeof(DumpRec), recs.size(), out);
+            fclose(out);
+            printf("dumped %lu\n", recs.size());
+        }
+        if (argc > 10) {
+            vector<string> qs = load_reads(argv[10]);
+            uint64_t nk = 0, hits = 0, total = 0;
+            for (string &s : qs) {
+                if (s.size() < k) continue;
+                SuperKmerEnumerator en(s, k, m, params.dede);
+                vector<kmer_full> sk;
+                en.next(sk);
+                while (sk.size() > 0) {
+                    vector<uint8_t *> v = index.get_superkmer(sk);
+                    for (uint8_t *p : v) {
+                        nk++;
+                        if (p) { total += *p; hits++; }
+                    }
+                    sk.clear();
+                    en.next(sk);
+                }
+            }
+            printf("decoy %lu %lu %lu\n", nk, hits, total);
+        }
         return 0;
     }
     fprintf(stderr, "unknown mode\n");

@@ -37,7 +37,12 @@ def test_store_kernel_loads_a_slot_with_one_256_bit_request_and_prefetches(mode)
     assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in the store kernel"
 
 
-def test_enumerate_kernel_keeps_its_state_in_registers():
-    sass = _sass("_Z16enumerate_kernelILi4ELb0EEv11BriskParamsPKyS2_yy7EnumOut")
-    assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in enumerate_kernel<4, ringless>"
-    assert "DFMA" in sass  # the rolled decycling sums are double arithmetic, like DecyclingSet::memDouble
+@pytest.mark.parametrize("fun", ["_Z16enumerate_kernelILi63ELi21ELi4ELb0ELb0EEv11BriskParamsPKyS2_yy7EnumOut",
+                                 "_Z16enumerate_kernelILi31ELi15ELi2ELb1ELb0EEv11BriskParamsPKyS2_yy7EnumOut"])
+def test_enumerate_kernel_keeps_its_state_in_registers(fun):
+    sass = _sass(fun)
+    assert "enumerate_kernel" in sass
+    assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in " + fun
+    # the rolled decycling class is fixed-point integer arithmetic: the steady state holds no double
+    # multiply-add; double additions remain in the literal fallback (DecyclingSet::memDouble as written)
+    assert "IMAD.HI" in sass and "DFMA" not in sass

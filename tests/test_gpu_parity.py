@@ -35,7 +35,7 @@ def oracle_superkmers(c, reads):
     return sorted(out)
 
 
-@pytest.mark.parametrize("flags", [0, 2], ids=["rolled", "literal"])
+@pytest.mark.parametrize("flags", [0, 2, 8], ids=["rolled", "literal", "rolled_runtime_km"])
 @pytest.mark.parametrize("name", SMALL + SYNTH[:1] + SYNTH[1:2])
 def test_enumerate_matches_oracle(name, flags):
     from brisk_b200 import decode_records
@@ -52,7 +52,7 @@ def test_enumerate_matches_oracle(name, flags):
     assert list(sizes[:len(c["skmer_size_hist"])]) == c["skmer_size_hist"]
 
 
-@pytest.mark.parametrize("flags", [0, 2], ids=["rolled", "literal"])
+@pytest.mark.parametrize("flags", [0, 2, 8], ids=["rolled", "literal", "rolled_runtime_km"])
 @pytest.mark.parametrize("name", SMALL + SYNTH)
 def test_count_dump_matches_reference_golden(name, flags):
     c = G.case(name)
