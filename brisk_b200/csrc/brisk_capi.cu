@@ -449,7 +449,7 @@ static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
 template <int KT, int MT, int RW, bool RING, bool LIT>
 static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
     typedef typename KM<KT, MT>::hash_t hash_t;
-    size_t smem = (RING ? ((size_t)h->P.w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 * 8 : 0) + ENUM_POOL * sizeof(u64) +
+    size_t smem = (RING ? ((size_t)h->P.w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 * 8 : 0) + (ENUM_THREADS / 32) * ENUM_WPOOL * sizeof(u64) +
                   4 * h->P.m * sizeof(double) + 64 * (size_t)h->P.dec_groups * sizeof(int2);
     cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<KT, MT, RW, RING, LIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

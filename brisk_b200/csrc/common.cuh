@@ -56,13 +56,25 @@ __host__ __device__ __forceinline__ u64 bfc_mix(u64 key, u64 mask) {
 // the same on 32-bit registers, valid when mask < 2^32 (m <= 16): every step is masked, left
 // shifts and additions only carry upwards, right shifts act on already-masked values.
 __device__ __forceinline__ u32 bfc_mix32(u32 key, u32 mask) {
-    key = (~key + (key << 21)) & mask;
+    key = (key * 0x1fffffu - 1u) & mask;  // ~key + (key << 21) = key * (2^21 - 1) - 1
     key = key ^ key >> 24;
-    key = ((key + (key << 3)) + (key << 8)) & mask;
+    key = (key * 265u) & mask;            // key + (key << 3) + (key << 8)
     key = key ^ key >> 14;
-    key = ((key + (key << 2)) + (key << 4)) & mask;
+    key = (key * 21u) & mask;             // key + (key << 2) + (key << 4)
     key = key ^ key >> 28;
-    key = (key + (key << 31)) & mask;
+    key = (key * 0x80000001u) & mask;     // key + (key << 31)
+    return key;
+}
+// bfc_mix with its shift-and-add rounds written as the multiplications they are (identical modulo 2^64): the
+// enumeration kernel is bound by the integer ALU pipe (shifts, logic ops, adds), multiplies run on the FMA pipe
+__device__ __forceinline__ u64 bfc_mix_mul(u64 key, u64 mask) {
+    key = (key * 0x1fffffull - 1ull) & mask;
+    key = key ^ key >> 24;
+    key = (key * 265ull) & mask;
+    key = key ^ key >> 14;
+    key = (key * 21ull) & mask;
+    key = key ^ key >> 28;
+    key = (key * 0x80000001ull) & mask;
     return key;
 }
 

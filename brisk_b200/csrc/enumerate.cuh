@@ -19,7 +19,8 @@
 #include "common.cuh"
 
 #define ENUM_THREADS 128
-#define ENUM_POOL 384
+#define ENUM_WPOOL 128   // superkmer descriptors staged per warp
+#define ENUM_WFLUSH 64   // a warp expands its staged descriptors into records once it holds this many
 #define ENUM_SYNC_STEPS 32
 
 // ---------------------------------------------------------------------------------------------
@@ -71,7 +72,7 @@ struct KM {
     }
     __device__ __forceinline__ static mer_t mix(mer_t key, mer_t mask) {
         if (sizeof(mer_t) == 4) return (mer_t)bfc_mix32((u32)key, (u32)mask);
-        return (mer_t)bfc_mix((u64)key, (u64)mask);
+        return (mer_t)bfc_mix_mul((u64)key, (u64)mask);
     }
     // rcbc (brisk/Kmers.cpp:320-332) on an m-mer
     __device__ __forceinline__ static mer_t rc(mer_t v, int m) {
@@ -101,24 +102,24 @@ __device__ __forceinline__ u32 warp_min(u32 v) { return __reduce_min_sync(0xffff
 // starting at p.  The two code bit planes are kept apart (code = a + 2b) because the reverse strand's sum is
 // w^(-1) conj(A - 2B).  Whenever |R| or |R(rot)| is inside the threshold band (eps + the worst-case fixed-point
 // error, P.dec_th) the literal double summation decides: the class is always the reference's.
-struct DecRot { int c30, s30; };
 __device__ __forceinline__ int dec_im(int Xr, int Xi, int c30, int s30) { return __mulhi(Xi, c30) - __mulhi(Xr, s30); }
 
-// class from the two bit-plane sums; rot_p / rot_q: cos, sin (2^30) of 2 pi p / m and 2 pi (p - 1) / m, p = start of the m-mer
-__device__ __forceinline__ u32 dec_class_rolled(int Ar, int Ai, int Br, int Bi, bool rv, int pc, int ps, int qc, int qs, int th,
-                                                bool &ambiguous) {
-    const int Xr = rv ? Ar - 2 * Br : Ar + 2 * Br, Xi = rv ? Ai - 2 * Bi : Ai + 2 * Bi;
-    const int D0 = dec_im(Xr, Xi, pc, ps);  // Im(w^-p X)
-    const int D1 = dec_im(Xr, Xi, qc, qs);  // Im(w^(1-p) X)
-    const int R = rv ? -D1 : D0, R2 = rv ? -D0 : D1;
-    ambiguous = min(abs(R), abs(R2)) <= th;
-    return R > 0 ? (R2 < 0 ? 0u : 2u) : (R2 > 0 ? 1u : 2u);
+// Class from D0 = Im(w^-p X), D1 = Im(w^(1-p) X), X = A + 2B (forward strand canonical) or A - 2B (reverse strand).
+// Forward: R = D0, R(rot) = D1.  Reverse: R = -D1, R(rot) = -D0.  Either way the class is 0 when D0 > 0 > D1, 1 when
+// D0 < 0 < D1 and 2 otherwise, and the band test is symmetric too.
+__device__ __forceinline__ u32 dec_class_signs(int D0, int D1, int th, bool &ambiguous) {
+    ambiguous = (u32)(D0 + th) <= 2u * (u32)th || (u32)(D1 + th) <= 2u * (u32)th;
+    return ((D0 ^ D1) < 0) ? (D1 > 0 ? 1u : 0u) : 2u;
 }
 
 // class of an arbitrary m-mer from the grouped tables: tab[g][v] = fixed-point sum of code * w^(left position) over the
 // three nucleotides 3g .. 3g+2 (from the right end) of the m-mer
 template <int MT>
 __device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double *coef, const int2 *tab, u64 seq, int m) {
+    // Only the last nucleotide set (the zero-padded tops of a truncated k-mer are mostly of this kind, Q3): R(rot) is the
+    // empty sum, exactly 0, which no fixed-point band can tell from +-1e-6.  memDouble gives R = -code sin(2 pi / m) <
+    // -eps and R(rot) = 0 > -eps: class 1; the all-A m-mer has R = 0: class 2.
+    if (seq < 4) return seq ? 1u : 2u;
     int Sr = 0, Si = 0;
     constexpr int G = MT ? (MT + 2) / 3 : 11;
 #pragma unroll
@@ -129,15 +130,15 @@ __device__ __forceinline__ u32 dec_class_tab(const BriskParams &P, const double 
             Si += e.y;
         }
     }
-    const int R = Si >> 2, R2 = __mulhi(Sr, P.rot1_s30) + __mulhi(Si, P.rot1_c30);
-    if (min(abs(R), abs(R2)) <= P.dec_th) return dec_mem_double(coef, P.eps, seq, m);
-    return R > 0 ? (R2 < 0 ? 0u : 2u) : (R2 > 0 ? 1u : 2u);
+    bool amb;
+    const u32 cls = dec_class_signs(Si >> 2, __mulhi(Sr, P.rot1_s30) + __mulhi(Si, P.rot1_c30), P.dec_th, amb);
+    return amb ? dec_mem_double(coef, P.eps, seq, m) : cls;
 }
 
 // ---------------------------------------------------------------------------------------------
 // superkmer descriptor staged in shared memory
-__device__ __forceinline__ u64 make_desc(u32 i0, int n, int pos0, bool rev, int tid) {
-    return (u64)i0 | ((u64)n << 32) | ((u64)pos0 << 40) | ((u64)rev << 48) | ((u64)tid << 49);
+__device__ __forceinline__ u64 make_desc(u32 i0, int n, int pos0, int rev, int lane) {
+    return (u64)i0 | ((u64)(u32)n << 32) | ((u64)(u32)pos0 << 40) | ((u64)(u32)rev << 48) | ((u64)(u32)lane << 49);
 }
 
 // Builds the packed record of one superkmer: k-mers i0 .. i0+n-1 of the read (read order), whose first
@@ -221,6 +222,10 @@ __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_T
 //               position from the requester's last 32 bases, which k > 32 has to do anyway for most positions (the
 //               64-bit truncation of get_minimizer, Q3); no order hash is computed before the first k-mer is complete.
 // LIT  = true : DecyclingSet::memDouble evaluated literally for every m-mer (BRISK_F_LITERAL_DECYCLE).
+//
+// The warps of a CTA only share the read-only tables: every warp stages the descriptors of its own superkmers (slots
+// handed out with a ballot, no atomics) and expands them into records on its own, so there is no CTA barrier after
+// the tables are loaded.
 template <int KT, int MT, int RW, bool RING, bool LIT>
 __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 read0, u64 n_reads,
@@ -233,17 +238,15 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     const int w = k - m + 1;
     const mer_t m_mask = C::m_mask(P);
     hash_t *ring = reinterpret_cast<hash_t *>(smem);   // [w][ENUM_THREADS] order hashes of the last w m-mers (RING only)
-    u64 *pool = smem + (RING ? ((size_t)w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 : 0);  // [ENUM_POOL] superkmer descriptors
-    double *coef = (double *)(pool + ENUM_POOL);       // [4m]
+    u64 *pool = smem + (RING ? ((size_t)w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 : 0);  // [warps][ENUM_WPOOL] superkmer descriptors
+    double *coef = (double *)(pool + (ENUM_THREADS / 32) * ENUM_WPOOL);  // [4m]
     int2 *dtab = (int2 *)(coef + 4 * m);               // [dec_groups][64] grouped decycling weights
-    __shared__ u32 pool_n;
-    __shared__ u32 s_maxL;
-    __shared__ u64 s_base;
-    __shared__ u64 rd_start[ENUM_THREADS];
-    __shared__ u64 rd_id[ENUM_THREADS];
 
+    const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
+    const u32 lane_lt = (1u << lane) - 1u;
+    u64 *wpool = pool + (tid >> 5) * ENUM_WPOOL;
     const u64 rid = read0 + (u64)blockIdx.x * ENUM_THREADS + tid;  // this launch covers reads [read0, n_reads) of the batch
     u32 L = 0;
     u64 wstart = 0;
@@ -254,72 +257,100 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
         L = (len >= (u64)k && len <= 0xffffffffull) ? (u32)len : 0u;  // apps/counter.cpp:233
     }
     const u64 *pk = packed + wstart;
-    rd_start[tid] = wstart;
-    rd_id[tid] = rid;
-    if (tid == 0) { pool_n = 0; s_maxL = 0; }
     for (int i = tid; i < 4 * m; i += ENUM_THREADS) coef[i] = P.coef[i];
     for (int i = tid; i < 64 * P.dec_groups; i += ENUM_THREADS) dtab[i] = P.dec_tab[i];
     __syncthreads();
-    atomicMax(&s_maxL, L);
-    __syncthreads();
-    const u32 maxL = s_maxL;
+    const u32 maxL = __reduce_max_sync(FULL, L);
+    const u32 minL = __reduce_min_sync(FULL, L ? L : 0xffffffffu);  // first step at which a read of the warp ends
+    if (maxL == 0) return;
 
     // rolling state
     mer_t f = 0, r = 0;
     u64 word = 0, revbits = 0, hist = 0;  // hist: the last 32 bases (RING = false)
-    int Ar = 0, Ai = 0, Br = 0, Bi = 0;   // bit-plane sums of the window, absolute phase (fixed point)
+    int Pr = 0, Pi = 0, Mr = 0, Mi = 0;   // window sums of code * w^(u mod m) and of (a - 2b) * w^(u mod m), fixed point
     int rslot = -1;           // ring slot of the newest m-mer (the same for every thread: all reads start at t = 0)
     int q = 0;                // t mod m (the same for every thread)
     hash_t H = 0;             // mini_hash
     int pos = 0;              // mini_pos
-    bool rev = false;         // reversed
+    int rev = 0;              // reversed
     u32 i0 = 0;               // first k-mer of the open superkmer
     int pos0 = 0;             // mini_pos of that k-mer
+    int pcount = 0;           // descriptors staged by the warp (the same in every lane)
     const int rshift = 2 * m - 2;
     const hash_t polyA = C::make_hash((u32)(P.polyA_hash >> 62), (mer_t)(P.polyA_hash & (u64)m_mask));
 
-    auto append = [&](u32 a, int n, int p0, bool rv) {
-        u32 slot = atomicAdd(&pool_n, 1u);
-        if (slot < ENUM_POOL) {
-            pool[slot] = make_desc(a, n, p0, rv, tid);
-        } else {  // staging full: emit directly
-            u64 g = atomicAdd(out.rec_count, 1ull);
-            if (out.recs && g < out.rec_cap) {
-                u64 rec[RW];
-                build_record<KT, MT, RW>(P, pk, a, n, p0, rv, rec);
-                store_record<RW>(out.recs, g, rec);
-                if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rid] + a) << 1) | (u64)rv;
-            }
+    auto emit_record = [&](const u64 *rpk, u64 g, u64 d, u64 read_id) {
+        if (out.recs && g < out.rec_cap) {
+            const int rvd = (int)(d >> 48) & 1;
+            u64 rec[RW];
+            build_record<KT, MT, RW>(P, rpk, (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd != 0, rec);
+            store_record<RW>(out.recs, g, rec);
+            if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[read_id] + (u32)d) << 1) | (u64)rvd;
         }
     };
+    // stages the descriptor of every lane that wants one
+    auto append = [&](bool want, u64 desc) {
+        const unsigned mk = __ballot_sync(FULL, want);
+        if (mk) {
+            if (want) {
+                const int slot = pcount + __popc(mk & lane_lt);
+                if (slot < ENUM_WPOOL) wpool[slot] = desc;
+                else emit_record(pk, atomicAdd(out.rec_count, 1ull), desc, rid);  // staging full: emit directly
+            }
+            pcount += __popc(mk);
+        }
+    };
+    // the warp expands its staged descriptors into packed records
+    auto flush = [&]() {
+        const u32 cnt = pcount < ENUM_WPOOL ? (u32)pcount : (u32)ENUM_WPOOL;
+        u64 base = 0;
+        if (lane == 0) base = atomicAdd(out.rec_count, (u64)cnt);
+        base = __shfl_sync(FULL, base, 0);
+        __syncwarp();
+        for (u32 e0 = 0; e0 < cnt; e0 += 32) {
+            const u32 e = e0 + lane;
+            const u64 d = e < cnt ? wpool[e] : 0ull;
+            const int owner = (int)(d >> 49) & 31;
+            const u64 o_start = __shfl_sync(FULL, wstart, owner);
+            const u64 o_rid = __shfl_sync(FULL, rid, owner);
+            if (e < cnt) emit_record(packed + o_start, base + e, d, o_rid);
+        }
+        __syncwarp();
+        pcount = 0;
+    };
 
-    // one base: forward / reverse m-mer, last 32 bases, bit-plane sums
+    // one base: forward / reverse m-mer, last 32 bases, window sums
     auto roll = [&]() {
         const u32 code = (u32)(word >> 62);
         word <<= 2;
         const u32 leave = (u32)(f >> rshift) & 3u;
-        f = (mer_t)(((f << 2) | code) & m_mask);
-        r = (mer_t)((r >> 2) | ((mer_t)(code ^ 2u) << rshift));
-        if (!RING) hist = (hist << 2) | code;
+        const u32 ccode = code ^ 2u;
+        f = (mer_t)((f * 4 + code) & m_mask);
+        r = (mer_t)((r >> 2) | ((mer_t)ccode << rshift));
+        if (!RING) hist = hist * 4 + code;
         if (!LIT) {
-            const int da = (int)(code & 1u) - (int)(leave & 1u), db = (int)(code >> 1) - (int)(leave >> 1);
+            // code = a + 2b: X+ = sum of code * tw, X- = sum of (a - 2b) * tw, and a - 2b = (code ^ 2) - 2
+            const int dp = (int)code - (int)leave, dm = (int)ccode - (int)(leave ^ 2u);
             const int tc = P.dec_tw[q].x, ts = P.dec_tw[q].y;
-            Ar += da * tc; Ai += da * ts;
-            Br += db * tc; Bi += db * ts;
+            Pr += dp * tc; Pi += dp * ts;
+            Mr += dm * tc; Mi += dm * ts;
         }
     };
     // order hash of the newest m-mer (hashing.cpp:8-19); rv = it is the reverse strand that is canonical
-    auto order_hash = [&](bool &rv) -> hash_t {
-        rv = r < f;
-        const mer_t canon = rv ? r : f;
+    auto order_hash = [&](int &rv) -> hash_t {
+        const bool rvb = r < f;
+        rv = rvb;
+        const mer_t canon = rvb ? r : f;
         u32 cls;
         if (LIT) {
             cls = dec_mem_double(coef, P.eps, (u64)canon, m);
         } else {
             // the m-mer ending at base t starts at phase p = (t + 1) mod m = q + 1
             const int p = q + 1 == m ? 0 : q + 1;
+            const int Xr = rvb ? Mr : Pr, Xi = rvb ? Mi : Pi;
             bool amb;
-            cls = dec_class_rolled(Ar, Ai, Br, Bi, rv, P.dec_rot[p].x, P.dec_rot[p].y, P.dec_rot[q].x, P.dec_rot[q].y, P.dec_th, amb);
+            cls = dec_class_signs(dec_im(Xr, Xi, P.dec_rot[p].x, P.dec_rot[p].y), dec_im(Xr, Xi, P.dec_rot[q].x, P.dec_rot[q].y),
+                                  P.dec_th, amb);
             if (amb) cls = dec_mem_double(coef, P.eps, (u64)canon, m);
         }
         return C::make_hash(cls, C::mix(canon, m_mask));
@@ -336,8 +367,8 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
         while (req) {
             const int src = __ffs(req) - 1;
             req &= req - 1;
-            const u64 s_cur = (!RING || kk > 32) ? __shfl_sync(0xffffffffu, cur64, src) : 0ull;
-            const u64 s_revbits = RING ? __shfl_sync(0xffffffffu, revbits, src) : 0ull;
+            const u64 s_cur = (!RING || kk > 32) ? __shfl_sync(FULL, cur64, src) : 0ull;
+            const u64 s_revbits = RING ? __shfl_sync(FULL, revbits, src) : 0ull;
             const int s_tid = (tid & ~31) | src;
             hash_t nh = (hash_t)~(hash_t)0;
             bool prv = false;
@@ -359,11 +390,11 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
             }
             hash_t hm = warp_min(nh);
             if (has_hi && polyA < hm) hm = polyA;
-            u64 tmask = __ballot_sync(0xffffffffu, nh == hm);
+            u64 tmask = __ballot_sync(FULL, nh == hm);
             if (has_hi && polyA == hm) tmask |= ((((u64)1) << (nmax - 31)) - 1) << 32;
-            const unsigned rvlo = __ballot_sync(0xffffffffu, prv);
+            const unsigned rvlo = __ballot_sync(FULL, prv);
             int mp = __ffsll((long long)tmask) - 1;
-            bool rv0 = mp < 32 ? (rvlo >> mp) & 1u : false;
+            int rv0 = mp < 32 ? (int)((rvlo >> mp) & 1u) : 0;
             u64 rest = tmask & (tmask - 1);
             if (rest) {  // equal hashes in the window: the tie rules of Kmers.cpp:389-404, in scan order
                 int cs = 0;
@@ -373,13 +404,13 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                     u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
                     cs = canonized128(lo, hi, kk) ? 1 : 0;
                 }
-                cs = __shfl_sync(0xffffffffu, cs, src);
+                cs = __shfl_sync(FULL, cs, src);
                 while (rest) {
                     const int i2 = __ffsll((long long)rest) - 1;
                     rest &= rest - 1;
-                    const bool rvi = i2 < 32 ? (rvlo >> i2) & 1u : false;
+                    const int rvi = i2 < 32 ? (int)((rvlo >> i2) & 1u) : 0;
                     if (nmax - i2 < mp) { mp = nmax - i2; rv0 = rvi; }
-                    else if (nmax - i2 == mp) { if (!cs) rv0 = false; }
+                    else if (nmax - i2 == mp) { if (!cs) rv0 = 0; }
                 }
             }
             if (lane == src) { H = hm; pos = mp; rev = rv0; }
@@ -407,7 +438,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                 rslot = rslot + 1 == w ? 0 : rslot + 1;
                 if (L) {
                     roll();
-                    bool rv;
+                    int rv;
                     ring[ring_at(rslot, tid)] = order_hash(rv);
                     revbits = (revbits << 1) | (u64)rv;
                 }
@@ -419,22 +450,24 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
             if (L) {
                 roll();
                 if (RING && t + 1 >= (u32)m) {
-                    bool rv;
+                    int rv;
                     ring[ring_at(rslot, tid)] = order_hash(rv);
                     revbits = (revbits << 1) | (u64)rv;
                 }
             }
             __syncwarp();
-            const unsigned req = __ballot_sync(0xffffffffu, L != 0);
+            const unsigned req = __ballot_sync(FULL, L != 0);
             if (req) rescans(req, k - 1, t);
             next_q();
             t++;
         }
         for (; t < t1; t++) {
             const bool active = t < L;
+            const bool first = t + 1 == (u32)k;  // the read's first k-mer never closes a superkmer (Kmers.cpp:585-593)
             hash_t h = 0;
-            bool rv = false, need = false;
-            const bool old_rev = rev;
+            int rv = 0;
+            bool need = false;
+            const int old_rev = rev;
             if (RING) rslot = rslot + 1 == w ? 0 : rslot + 1;
             if (active) {
                 roll();
@@ -447,50 +480,28 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
                 need = pos > k - m;  // the minimizer left the window (Kmers.cpp:551-562)
             }
             __syncwarp();
-            const unsigned req = __ballot_sync(0xffffffffu, need);
+            const unsigned req = __ballot_sync(FULL, need);
             if (req) rescans(req, k, t);
+            const u32 i = t + 1 - k;
+            bool emit = false;
+            u64 desc = 0;
             if (active) {
-                const u32 i = t + 1 - k;
                 bool boundary = need;
-                if (!boundary && h < H) {
+                if (!need && h < H) {
                     boundary = true;
                     H = h; pos = 0; rev = rv;
                 }
-                if (i == 0) {
-                    pos0 = pos;
-                } else if (boundary) {
-                    append(i0, (int)(i - i0), pos0, old_rev);
+                if (boundary || first) {
+                    emit = !first;
+                    desc = make_desc(i0, (int)(i - i0), pos0, old_rev, lane);
                     i0 = i; pos0 = pos;
                 }
-                if (t + 1 == L) append(i0, (int)(i + 1 - i0), pos0, rev);
             }
+            append(emit, desc);
+            if (t + 1 >= minL)  // some read of the warp may end here: its open superkmer is the last one
+                append(active && t + 1 == L, make_desc(i0, (int)(i + 1 - i0), pos0, rev, lane));
             next_q();
         }
-        __syncthreads();
-        const u32 cnt_raw = pool_n;
-        __syncthreads();  // nobody appends again before everyone has read the fill level
-        const bool last = t0 + ENUM_SYNC_STEPS >= maxL;
-        if (cnt_raw >= ENUM_POOL / 2 || (last && cnt_raw > 0)) {
-            const u32 cnt = cnt_raw < ENUM_POOL ? cnt_raw : ENUM_POOL;
-            if (tid == 0) s_base = atomicAdd(out.rec_count, (u64)cnt);
-            __syncthreads();
-            const u64 base = s_base;
-            if (out.recs) {
-                for (u32 e = tid; e < cnt; e += ENUM_THREADS) {
-                    u64 g = base + e;
-                    if (g >= out.rec_cap) break;
-                    u64 d = pool[e];
-                    int owner = (int)(d >> 49) & 127;
-                    bool rvd = (d >> 48) & 1;
-                    u64 rec[RW];
-                    build_record<KT, MT, RW>(P, packed + rd_start[owner], (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd, rec);
-                    store_record<RW>(out.recs, g, rec);
-                    if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[rd_id[owner]] + (u32)d) << 1) | (u64)rvd;
-                }
-            }
-            __syncthreads();
-            if (tid == 0) pool_n = 0;
-            __syncthreads();
-        }
+        if (pcount >= ENUM_WFLUSH || (t1 >= maxL && pcount > 0)) flush();
     }
 }
