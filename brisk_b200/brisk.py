@@ -129,6 +129,13 @@ class Brisk:
         order = np.argsort(occ >> np.uint64(1), kind="stable")
         return recs[order], occ[order]
 
+    def checksum(self):
+        """(sum of a 64-bit mix of every stored (kmer_s, minimizer_idx, DATA byte), sum of the DATA bytes, number of stored
+        k-mers) of this handle's shard; order-independent, the shards' sums add up to the unsharded index's."""
+        out = np.zeros(3, np.uint64)
+        self._check(self._lib.brisk_checksum(self._h, _ptr(out)))
+        return int(out[0]), int(out[1]), int(out[2])
+
     def count_reads(self, bases, offsets):
         self._check(self._lib.brisk_count_reads(self._h, _ptr(bases), _ptr(offsets), self._n_reads(offsets)))
 

@@ -82,6 +82,7 @@ struct brisk_handle {
     uint32_t *bucket_bits = nullptr;
     uint64_t bitmap_words = 0;
     unsigned char *data = nullptr;
+    uint32_t *cnt = nullptr;  // [cap + 64] counts beside the table (StoreView::cnt)
     u64 *overflow = nullptr;
     uint64_t ovf_cap = 0;
     uint64_t n_keys = 0, n_new_recs = 0;
@@ -193,6 +194,7 @@ static StoreView view_of(brisk_handle *h) {
     T.slots = h->slots;
     T.mask = h->cap - 1;
     T.special = h->special;
+    T.cnt = h->cnt;
     T.counters = h->counters;
     T.bucket_bits = h->bucket_bits;
     T.data = h->data;
@@ -204,7 +206,7 @@ static StoreView view_of(brisk_handle *h) {
 
 static size_t slot_bytes(const brisk_handle *h) { return h->P.key_words == 1 ? sizeof(Slot1) : sizeof(Slot2); }
 
-static int alloc_table(brisk_handle *h, uint64_t cap, void **slots, unsigned char **data) {
+static int alloc_table(brisk_handle *h, uint64_t cap, void **slots, unsigned char **data, uint32_t **cnt) {
     size_t bytes = cap * slot_bytes(h);
     if (h->flags & BRISK_F_MANAGED) CK(cudaMallocManaged(slots, bytes));
     else CK(cudaMalloc(slots, bytes));
@@ -212,6 +214,12 @@ static int alloc_table(brisk_handle *h, uint64_t cap, void **slots, unsigned cha
     if (h->P.key_words == 1) init_table_kernel<1><<<blocks, 256, 0, h->stream>>>(*slots, cap);
     else init_table_kernel<2><<<blocks, 256, 0, h->stream>>>(*slots, cap);
     CK(cudaGetLastError());
+    {
+        size_t cb = (cap + 64) * sizeof(uint32_t);
+        if (h->flags & BRISK_F_MANAGED) CK(cudaMallocManaged((void **)cnt, cb));
+        else CK(cudaMalloc((void **)cnt, cb));
+        CK(cudaMemsetAsync(*cnt, 0, cb, h->stream));
+    }
     *data = nullptr;
     if (h->data_size > 1) {
         size_t db = (cap + 64) * (size_t)h->data_size;
@@ -226,26 +234,31 @@ static int grow_to(brisk_handle *h, uint64_t new_cap) {
     if (new_cap <= h->cap) return BRISK_OK;
     void *ns = nullptr;
     unsigned char *nd = nullptr;
-    int rc = alloc_table(h, new_cap, &ns, &nd);
+    uint32_t *nc = nullptr;
+    int rc = alloc_table(h, new_cap, &ns, &nd, &nc);
     if (rc) return rc;
     if (h->slots) {
         StoreView from = view_of(h);
         StoreView to = from;
-        to.slots = ns; to.mask = new_cap - 1; to.data = nd;
+        to.slots = ns; to.mask = new_cap - 1; to.data = nd; to.cnt = nc;
         int blocks = (int)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
         if (h->P.key_words == 1) rehash_kernel<1><<<blocks, 256, 0, h->stream>>>(h->P, from, to);
         else rehash_kernel<2><<<blocks, 256, 0, h->stream>>>(h->P, from, to);
         CK(cudaGetLastError());
-        if (h->data) {  // DATA of the special key follows the arena's end
+        // counts (and DATA) of the special key follow the arena's end
+        CK(cudaMemcpyAsync(nc + new_cap, h->cnt + h->cap, 64 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, h->stream));
+        if (h->data) {
             CK(cudaMemcpyAsync(nd + new_cap * h->data_size, h->data + h->cap * h->data_size, 64 * (size_t)h->data_size,
                                cudaMemcpyDeviceToDevice, h->stream));
         }
         CK(cudaStreamSynchronize(h->stream));
         cudaFree(h->slots);
+        cudaFree(h->cnt);
         if (h->data) cudaFree(h->data);
     }
     h->slots = ns;
     h->data = nd;
+    h->cnt = nc;
     h->cap = new_cap;
     return BRISK_OK;
 }
@@ -333,6 +346,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaFree(h->d_part2);
     cudaFree(h->dec_tab);
     cudaFree(h->slots);
+    cudaFree(h->cnt);
     cudaFree(h->data);
     cudaFree(h->special);
     cudaFree(h->counters);
@@ -806,12 +820,19 @@ static int return_results(brisk_handle *h, const Exchange &X, uint64_t n_recs, b
 // or pass the hint (a hint that is too small must not stop the table from growing ahead of the batch: with the table
 // nearly full every insert walks to the probe limit and is parked).  The overflow arena is sized with the batch, so
 // that even a badly underestimated batch is parked and replayed, not dropped.
-static int pregrow(brisk_handle *h, uint64_t incoming) {
+// worst_case: the call hands slot ids / newly flags back, which a rehash during settle() would invalidate: besides the
+// estimate, make sure that even with every incoming k-mer new the load stays below 0.9, where nothing reaches the probe
+// limit, so that nothing is parked (a table that is merely re-queried with known keys does not grow for this).
+static int pregrow(brisk_handle *h, uint64_t incoming, bool worst_case = false) {
     uint64_t est_new = incoming;
     if (h->hint) {
         const uint64_t by_hint = std::min<uint64_t>(incoming, h->hint > h->n_keys ? h->hint - h->n_keys : 0);
         const uint64_t by_rate = std::min<uint64_t>(incoming, (uint64_t)((1.5 * h->new_rate + 0.02) * (double)incoming));
         est_new = std::max(by_hint, by_rate);
+    }
+    if (worst_case && (h->n_keys + incoming) * 10 > h->cap * 9) {
+        int rc = grow_to(h, pow2ceil((h->n_keys + incoming) * 2));
+        if (rc) return rc;
     }
     h->pending_incoming = incoming;
     h->keys_before = h->n_keys;
@@ -957,7 +978,7 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         if (rc) return rc;
         CK(cudaEventRecord(h->ev[3], h->stream));
         if (mode != MODE_GET) {
-            rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes);
+            rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes, with_occ);
             if (rc) return rc;
         }
         rc = stage_outputs();
@@ -1106,7 +1127,7 @@ static int run_kmers(brisk_handle *h, const brisk_kmer *kmers, uint64_t n, int m
         d_k = (const KmerIn *)h->d_kmers.p;
     }
     if (mode != MODE_GET) {
-        int rc = pregrow(h, n);
+        int rc = pregrow(h, n, slots != nullptr || flags != nullptr);
         if (rc) return rc;
     }
     bool s_dev = is_device_ptr(slots), f_dev = is_device_ptr(flags), d_dev = is_device_ptr(data_out);
@@ -1153,11 +1174,7 @@ extern "C" void *brisk_data_ptr(brisk_t *h, uint64_t slot) {
         if (cudaSetDevice(h->device) != cudaSuccess || settle_pending(h) != BRISK_OK) return nullptr;
     }
     if (slot == BRISK_NO_SLOT || slot >= h->cap + 64) return nullptr;
-    if (h->data_size == 1) {
-        if (slot >= h->cap) return (unsigned char *)(h->special + (slot - h->cap)) + 3;
-        size_t off = slot * slot_bytes(h) + (h->P.key_words == 1 ? offsetof(Slot1, meta) : offsetof(Slot2, meta)) + 3;
-        return (unsigned char *)h->slots + off;  // the DATA byte is the top byte of the little-endian meta word
-    }
+    if (h->data_size == 1) return (unsigned char *)(h->cnt + slot);  // the DATA byte is the low byte of the little-endian count word
     return h->data + slot * h->data_size;
 }
 
@@ -1289,7 +1306,7 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
     CK(cudaMemcpyAsync(&nb, h->counters + 4, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     uint64_t v[4] = {nb, h->n_new_recs, h->n_keys,
-                     h->cap * slot_bytes(h) + h->bitmap_words * 4 + h->ovf_cap * 24 + (h->data ? (h->cap + 64) * h->data_size : 0)};
+                     h->cap * slot_bytes(h) + (h->cap + 64) * 4 + h->bitmap_words * 4 + h->ovf_cap * 24 + (h->data ? (h->cap + 64) * h->data_size : 0)};
     if (h->comm && h->comm->n > 1) {  // buckets are disjoint over the ranks: the totals are sums
         u64 *tmp = part_matrix(h);
         CK(cudaMemcpyAsync(tmp, v, sizeof(v), cudaMemcpyHostToDevice, h->stream));
@@ -1302,6 +1319,45 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
     if (nb_kmers) *nb_kmers = v[2];
     if (largest_bucket) *largest_bucket = 0;
     if (device_bytes) *device_bytes = v[3];
+    return BRISK_OK;
+}
+
+// order-independent checksum of the stored set of this handle (this rank's shard): out[0] = sum of a 64-bit mix of every
+// (kmer_s, minimizer_idx, DATA byte), out[1] = sum of the DATA bytes, out[2] = number of stored k-mers
+extern "C" int brisk_checksum(brisk_t *h, uint64_t out[3]) {
+    if (!h || !out) return fail(BRISK_E_PARAM, "null argument");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
+    u64 *acc = part_matrix(h);  // scratch words
+    CK(cudaMemsetAsync(acc, 0, 3 * sizeof(uint64_t), h->stream));
+    unsigned blocks = (unsigned)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
+    if (h->P.key_words == 1) checksum_kernel<1><<<blocks, 256, 0, h->stream>>>(view_of(h), 64, acc);
+    else checksum_kernel<2><<<blocks, 256, 0, h->stream>>>(view_of(h), 64, acc);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, acc, 3 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return BRISK_OK;
+}
+
+// ---- synthetic reads on the device (synth.cuh): benchmark / test support.  `genome` and `out` are device pointers on
+// the current device; the kernels run on `stream` (cudaStream_t, NULL = the default stream) and are not waited for.
+extern "C" int brisk_synth_genome(void *genome, uint64_t G, uint64_t seed, void *stream) {
+    if (!genome || !is_device_ptr(genome)) return fail(BRISK_E_PARAM, "genome must be a device pointer");
+    if (G == 0) return BRISK_OK;
+    const uint64_t threads = (G + 15) / 16;
+    synth_genome_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>((unsigned char *)genome, G, seed);
+    CK(cudaGetLastError());
+    return BRISK_OK;
+}
+extern "C" int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uint64_t seed, uint64_t first, uint64_t count, void *out,
+                                 void *stream) {
+    if (!genome || !out || !is_device_ptr(genome) || !is_device_ptr(out)) return fail(BRISK_E_PARAM, "genome and out must be device pointers");
+    if (L == 0 || L > G) return fail(BRISK_E_PARAM, "need 0 < L <= G");
+    if (count == 0) return BRISK_OK;
+    synth_reads_kernel<<<(unsigned)((count * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const unsigned char *)genome, G, L, seed, first, count,
+                                                                                                (unsigned char *)out);
+    CK(cudaGetLastError());
     return BRISK_OK;
 }
 

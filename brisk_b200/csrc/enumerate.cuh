@@ -227,7 +227,7 @@ __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_T
 // handed out with a ballot, no atomics) and expands them into records on its own, so there is no CTA barrier after
 // the tables are loaded.
 template <int KT, int MT, int RW, bool RING, bool LIT>
-__global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
+__global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 read0, u64 n_reads,
                                                                  EnumOut out) {
     typedef KM<KT, MT> C;
@@ -270,8 +270,9 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
     int Pr = 0, Pi = 0, Mr = 0, Mi = 0;   // window sums of code * w^(u mod m) and of (a - 2b) * w^(u mod m), fixed point
     int rslot = -1;           // ring slot of the newest m-mer (the same for every thread: all reads start at t = 0)
     int q = 0;                // t mod m (the same for every thread)
+    const int DEAD_POS = -(1 << 30);
     hash_t H = 0;             // mini_hash
-    int pos = 0;              // mini_pos
+    int pos = L ? 0 : DEAD_POS;  // mini_pos
     int rev = 0;              // reversed
     u32 i0 = 0;               // first k-mer of the open superkmer
     int pos0 = 0;             // mini_pos of that k-mer
@@ -289,10 +290,11 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
         }
     };
     // stages the descriptor of every lane that wants one
-    auto append = [&](bool want, u64 desc) {
+    auto append = [&](bool want, u32 a, int n, int p0, int rv) {
         const unsigned mk = __ballot_sync(FULL, want);
         if (mk) {
             if (want) {
+                const u64 desc = make_desc(a, n, p0, rv, lane);
                 const int slot = pcount + __popc(mk & lane_lt);
                 if (slot < ENUM_WPOOL) wpool[slot] = desc;
                 else emit_record(pk, atomicAdd(out.rec_count, 1ull), desc, rid);  // staging full: emit directly
@@ -351,7 +353,7 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
             bool amb;
             cls = dec_class_signs(dec_im(Xr, Xi, P.dec_rot[p].x, P.dec_rot[p].y), dec_im(Xr, Xi, P.dec_rot[q].x, P.dec_rot[q].y),
                                   P.dec_th, amb);
-            if (amb) cls = dec_mem_double(coef, P.eps, (u64)canon, m);
+            if (amb && pos > DEAD_POS / 2) cls = dec_mem_double(coef, P.eps, (u64)canon, m);  // (not for a lane whose read has ended)
         }
         return C::make_hash(cls, C::mix(canon, m_mask));
     };
@@ -462,44 +464,35 @@ __global__ void __launch_bounds__(ENUM_THREADS) enumerate_kernel(const BriskPara
             t++;
         }
         for (; t < t1; t++) {
-            const bool active = t < L;
+            // a lane whose read has ended (or is too short) keeps rolling zeros with H = 0 and mini_pos far below zero: it
+            // can neither take over (h < 0) nor ask for a rescan, so the steady state needs no "active" predicate
             const bool first = t + 1 == (u32)k;  // the read's first k-mer never closes a superkmer (Kmers.cpp:585-593)
-            hash_t h = 0;
-            int rv = 0;
-            bool need = false;
             const int old_rev = rev;
             if (RING) rslot = rslot + 1 == w ? 0 : rslot + 1;
-            if (active) {
-                roll();
-                h = order_hash(rv);
-                if (RING) {
-                    ring[ring_at(rslot, tid)] = h;
-                    revbits = (revbits << 1) | (u64)rv;
-                }
-                pos += 1;
-                need = pos > k - m;  // the minimizer left the window (Kmers.cpp:551-562)
+            roll();
+            int rv;
+            const hash_t h = order_hash(rv);
+            if (RING) {
+                ring[ring_at(rslot, tid)] = h;
+                revbits = (revbits << 1) | (u64)rv;
             }
-            __syncwarp();
-            const unsigned req = __ballot_sync(FULL, need);
+            pos += 1;
+            const unsigned req = __ballot_sync(FULL, pos > k - m);  // the minimizer left the window (Kmers.cpp:551-562)
+            const bool need = (req >> lane) & 1u;
             if (req) rescans(req, k, t);
             const u32 i = t + 1 - k;
-            bool emit = false;
-            u64 desc = 0;
-            if (active) {
-                bool boundary = need;
-                if (!need && h < H) {
-                    boundary = true;
-                    H = h; pos = 0; rev = rv;
-                }
-                if (boundary || first) {
-                    emit = !first;
-                    desc = make_desc(i0, (int)(i - i0), pos0, old_rev, lane);
-                    i0 = i; pos0 = pos;
-                }
+            bool boundary = need;
+            if (!need && h < H) {
+                boundary = true;
+                H = h; pos = 0; rev = rv;
             }
-            append(emit, desc);
-            if (t + 1 >= minL)  // some read of the warp may end here: its open superkmer is the last one
-                append(active && t + 1 == L, make_desc(i0, (int)(i + 1 - i0), pos0, rev, lane));
+            append(boundary && !first, i0, (int)(i - i0), pos0, old_rev);
+            if (boundary || first) { i0 = i; pos0 = pos; }
+            if (t + 1 >= minL) {  // some read of the warp may end here: its open superkmer is the last one
+                const bool fin = t + 1 == L;
+                append(fin, i0, (int)(i + 1 - i0), pos0, rev);
+                if (fin) { H = 0; pos = DEAD_POS; }
+            }
             next_q();
         }
         if (pcount >= ENUM_WFLUSH || (t1 >= maxL && pcount > 0)) flush();

@@ -7,19 +7,22 @@
 //
 //   KW = 1 (2k <= 64):  16-byte slot  { u64 key;      u32 meta; u32 aux;          }   two per 32-B sector
 //   KW = 2           :  32-byte slot  { u64 lo, hi;   u32 meta; u32 aux; u64 aux2 }   one per sector
-//   meta = (minimizer_idx + 1) in bits 0..7 (0 = claimed but not yet published), DATA byte (the
-//          counter's uint8_t) in bits 24..31 so that the wrapping ++ is a single atomicAdd(1<<24).
+//   meta = (minimizer_idx + 1) in bits 0..7 (0 = claimed but not yet published).
+//   cnt[slot] (a dense u32 array beside the table): the counter's DATA.  The reference's uint8_t wraps at 256
+//          (apps/counter.cpp:262-269); a u32 that is only ever incremented and read modulo 256 is exactly that,
+//          and the ++ is one fire-and-forget red.add on a word that shares its 32-byte sector with the counts
+//          of the neighbouring k-mers of the same superkmer: a found k-mer no longer dirties its slot's sector.
 //
 // insert = CAS-claim of the key word(s) (atomicCAS / atom.cas.b128), then one atomicAdd publishes the
-// idx tag and applies the first count.  A slot never moves until the table is rehashed, so the slot
-// index is the stable DATA handle that replaces the reference's realloc + protect_data.
+// idx tag.  A slot never moves until the table is rehashed, so the slot index is the stable DATA handle
+// that replaces the reference's realloc + protect_data.
 #pragma once
 #include "common.cuh"
+#include "synth.cuh"
 
 #define STORE_EMPTY (~0ull)
 #define STORE_MAX_PROBE 8192u
 #define META_TAG_MASK 0xFFu
-#define META_COUNT_ONE (1u << 24)
 
 struct Slot1 { u64 key; u32 meta; u32 aux; };
 struct Slot2 { u64 lo, hi; u32 meta; u32 aux; u64 aux2; };
@@ -28,6 +31,7 @@ struct StoreView {
     void *slots;        // Slot1[cap] or Slot2[cap]
     u64 mask;           // cap - 1
     u32 *special;       // [64] meta words of the one key that equals the empty pattern (poly-G at k = 32 / 64)
+    u32 *cnt;           // [cap + 64] counts (DATA of the counter, modulo 256); [cap + idx] belongs to special[idx]
     u64 *counters;      // [0] stored k-mers, [1] failed inserts, [2] records whose first k-mer was new, [3] dump cursor
     u32 *bucket_bits;   // 4^b bits: bucket ids in use (null = not tracked)
     unsigned char *data;  // DATA arena for data_size > 1 (null otherwise)
@@ -69,18 +73,17 @@ __device__ __forceinline__ u32 *slot_meta_ptr(const StoreView &T, u64 slot) {
     return &reinterpret_cast<S *>(T.slots)[slot].meta;
 }
 
-// find-or-claim (kmer_s, idx).  add = increment applied to meta (META_COUNT_ONE for the counter, 0 for a
-// plain insert).  Returns 0 = found, 1 = newly inserted, -1 = probe limit reached (nothing changed).
+// find-or-claim (kmer_s, idx).  add = increment applied to the count (1 for the counter, 0 for a plain insert).
+// Returns 0 = found, 1 = newly inserted, -1 = probe limit reached (nothing changed).
 template <int KW>
 __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, u32 idx, u32 add, u64 home, u64 &slot_out) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
-        u32 old = atomicAdd(T.special + idx, add);
-        int res = 0;
-        if ((old & META_TAG_MASK) == 0) res = (atomicOr(T.special + idx, tag) & META_TAG_MASK) == 0 ? 1 : 0;
+        const u32 old = atomicOr(T.special + idx, tag);
         slot_out = T.mask + 1 + idx;
-        return res;
+        if (add) atomicAdd(T.cnt + slot_out, add);
+        return (old & META_TAG_MASK) == 0 ? 1 : 0;
     }
     S *tab = reinterpret_cast<S *>(T.slots);
     u64 s = home;
@@ -98,7 +101,8 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
             if (cur == STORE_EMPTY) {
                 u64 old = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo);
                 if (old == STORE_EMPTY) {
-                    atomicAdd(&p->meta, tag | add);
+                    atomicAdd(&p->meta, tag);
+                    if (add) atomicAdd(T.cnt + s, add);
                     slot_out = s;
                     return 1;
                 }
@@ -114,7 +118,8 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
                 u64 olo, ohi;
                 cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
                 if (olo == STORE_EMPTY && ohi == STORE_EMPTY) {
-                    atomicAdd(&p->meta, tag | add);
+                    atomicAdd(&p->meta, tag);
+                    if (add) atomicAdd(T.cnt + s, add);
                     slot_out = s;
                     return 1;
                 }
@@ -127,7 +132,7 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
             u32 t = mt & META_TAG_MASK;
             if (t == 0) continue;  // claimed by another thread, tag not published yet: look again
             if (t == tag) {
-                if (add) atomicAdd(&p->meta, add);
+                if (add) atomicAdd(T.cnt + s, add);
                 slot_out = s;
                 return 0;
             }
@@ -138,7 +143,7 @@ __device__ __forceinline__ int store_upsert(const StoreView &T, u64 lo, u64 hi, 
     return -1;
 }
 
-// lookup only; returns true and the slot when present
+// lookup only; returns true, the slot and its count word (meta_out) when present
 template <int KW>
 __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 home, u64 &slot_out, u32 &meta_out) {
     typedef typename SlotOf<KW>::type S;
@@ -146,7 +151,7 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
     if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {
         u32 mt = ld_cg32(T.special + idx);
         slot_out = T.mask + 1 + idx;
-        meta_out = mt;
+        meta_out = ld_cg32(T.cnt + slot_out);
         return (mt & META_TAG_MASK) == tag;
     }
     const S *tab = reinterpret_cast<const S *>(T.slots);
@@ -171,7 +176,7 @@ __device__ __forceinline__ bool store_find(const StoreView &T, u64 lo, u64 hi, u
         if (match) {
             u32 t = mt & META_TAG_MASK;
             if (t == 0) continue;
-            if (t == tag) { slot_out = s; meta_out = mt; return true; }
+            if (t == tag) { slot_out = s; meta_out = ld_cg32(T.cnt + s); return true; }
         }
         probes++;
         s = probe_slot(home, lo, KW == 1 ? 0 : hi, idx, probes, T.mask);
@@ -229,10 +234,9 @@ enum { PR_FOUND = 0, PR_NEW = 1, PR_ABSENT = 2, PR_NEXT = 3, PR_AGAIN = 4 };
 // one probe of slot s for (lo, hi, idx).  MODE_GET never writes.  PR_NEXT: the slot holds another key; PR_AGAIN: the
 // slot holds this k-mer's key words but its tag is not published yet — look at the same slot again.
 template <int KW, int MODE>
-__device__ __forceinline__ int probe_once(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 s, u32 &meta_out) {
+__device__ __forceinline__ int probe_once(const StoreView &T, u64 lo, u64 hi, u32 idx, u64 s) {
     typedef typename SlotOf<KW>::type S;
     const u32 tag = idx + 1;
-    const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
     S *p = reinterpret_cast<S *>(T.slots) + s;
     u64 clo, chi;
     u32 mt;
@@ -245,7 +249,8 @@ __device__ __forceinline__ int probe_once(const StoreView &T, u64 lo, u64 hi, u3
         if (KW == 1) olo = atomicCAS(reinterpret_cast<u64 *>(p), STORE_EMPTY, lo);
         else cas128(p, STORE_EMPTY, STORE_EMPTY, lo, hi, olo, ohi);
         if (olo == STORE_EMPTY && ohi == STORE_EMPTY) {
-            atomicAdd(&p->meta, tag | add);
+            atomicAdd(&p->meta, tag);
+            if (MODE == MODE_COUNT) atomicAdd(T.cnt + s, 1u);
             return PR_NEW;
         }
         // somebody else claimed the slot meanwhile: same key words -> wait for its tag, else move on
@@ -255,8 +260,7 @@ __device__ __forceinline__ int probe_once(const StoreView &T, u64 lo, u64 hi, u3
         const u32 t = mt & META_TAG_MASK;
         if (t == 0) return PR_AGAIN;
         if (t == tag) {
-            if (add) atomicAdd(&p->meta, add);
-            meta_out = mt;
+            if (MODE == MODE_COUNT) atomicAdd(T.cnt + s, 1u);
             return PR_FOUND;
         }
     }
@@ -293,29 +297,38 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
     u64 agg_hits = 0, agg_sum = 0;
     int qn = 0;  // queue length (warp-uniform)
 
+    // MODE_GET: the count word of a hit is requested when the hit is known and consumed one probe round later, after
+    // that round's slot load has come back, so that it never adds a second dependent round trip to a step
+    bool pend_hit = false;
+    u32 pend_cv = 0;
+    u64 pend_oi = 0;
+    auto consume_count = [&]() {
+        if (MODE == MODE_GET && pend_hit) {
+            agg_sum += pend_cv & 0xffu;
+            if (O.rec_occ && O.data && T.data_size == 1) O.data[pend_oi] = (unsigned char)pend_cv;
+        }
+        pend_hit = false;
+    };
     // one probe round over the k-mers the lanes hold; unsettled ones go (back) to the queue
     auto round = [&](bool active, u64 lo, u64 hi, u64 home, u64 oi, u32 misc) {
         int res = PR_NEXT;
-        u32 mt = 0;
         u64 slot = ~0ull;
         if (active) {
             const u32 idx = misc & 0xffu, probes = misc >> 16;
             if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) {  // the key that equals the empty pattern
                 slot = T.mask + 1 + idx;
                 if (MODE == MODE_GET) {
-                    mt = ld_cg32(T.special + idx);
-                    res = (mt & META_TAG_MASK) == idx + 1 ? PR_FOUND : PR_ABSENT;
+                    res = (ld_cg32(T.special + idx) & META_TAG_MASK) == idx + 1 ? PR_FOUND : PR_ABSENT;
                 } else {
-                    u32 old = atomicAdd(T.special + idx, MODE == MODE_COUNT ? META_COUNT_ONE : 0u);
-                    res = PR_FOUND;
-                    if ((old & META_TAG_MASK) == 0) res = (atomicOr(T.special + idx, idx + 1) & META_TAG_MASK) == 0 ? PR_NEW : PR_FOUND;
+                    res = (atomicOr(T.special + idx, idx + 1) & META_TAG_MASK) == 0 ? PR_NEW : PR_FOUND;
+                    if (MODE == MODE_COUNT) atomicAdd(T.cnt + slot, 1u);
                 }
             } else if (probes >= STORE_MAX_PROBE) {
                 res = PR_ABSENT;  // probe limit: parked (insert) / absent (get)
-                if (MODE != MODE_GET) store_park(T, lo, hi, idx, MODE == MODE_COUNT ? META_COUNT_ONE : 0u);
+                if (MODE != MODE_GET) store_park(T, lo, hi, idx, MODE == MODE_COUNT ? 1u : 0u);
             } else {
                 slot = probe_slot(home, lo, KW == 1 ? 0 : hi, idx, probes, T.mask);
-                res = probe_once<KW, MODE>(T, lo, hi, idx, slot, mt);
+                res = probe_once<KW, MODE>(T, lo, hi, idx, slot);
             }
         }
         const bool again = active && res >= PR_NEXT;
@@ -329,28 +342,32 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
             S.q_misc[q] = res == PR_NEXT ? misc + (1u << 16) : misc;
         }
         qn += __popc(am);
-        if (active && !again) {
-            const bool hit = res == PR_FOUND;
-            if (MODE == MODE_GET) {
-                if (hit) { agg_hits++; agg_sum += mt >> 24; }
-                if (O.rec_occ) {
-                    if (O.flags) O.flags[oi] = hit;
-                    if (O.slots) O.slots[oi] = hit ? slot : ~0ull;
-                    if (O.data) {
-                        if (T.data_size == 1) O.data[oi] = hit ? (unsigned char)(mt >> 24) : 0;
-                        else for (u32 q = 0; q < T.data_size; q++)
-                            O.data[oi * T.data_size + q] = hit ? T.data[slot * T.data_size + q] : 0;
-                    }
+        if (MODE == MODE_GET) {
+            consume_count();
+            const bool hit = active && !again && res == PR_FOUND;
+            if (hit) {
+                agg_hits++;
+                pend_cv = ld_relaxed32(T.cnt + slot);
+                pend_hit = true;
+                pend_oi = oi;
+            }
+            if (active && !again && O.rec_occ) {
+                if (O.flags) O.flags[oi] = hit;
+                if (O.slots) O.slots[oi] = hit ? slot : ~0ull;
+                if (O.data) {
+                    if (T.data_size == 1) { if (!hit) O.data[oi] = 0; }
+                    else for (u32 q = 0; q < T.data_size; q++)
+                        O.data[oi * T.data_size + q] = hit ? T.data[slot * T.data_size + q] : 0;
                 }
-            } else {
-                if (res == PR_NEW) {
-                    new_keys++;
-                    if (misc & 0x100u) new_recs++;
-                }
-                if (O.rec_occ) {
-                    if (O.flags) O.flags[oi] = res == PR_NEW;
-                    if (O.slots) O.slots[oi] = res == PR_ABSENT ? ~0ull : slot;
-                }
+            }
+        } else if (active && !again) {
+            if (res == PR_NEW) {
+                new_keys++;
+                if (misc & 0x100u) new_recs++;
+            }
+            if (O.rec_occ) {
+                if (O.flags) O.flags[oi] = res == PR_NEW;
+                if (O.slots) O.slots[oi] = res == PR_ABSENT ? ~0ull : slot;
             }
         }
     };
@@ -468,6 +485,7 @@ __global__ void __launch_bounds__(256) records_kernel(const BriskParams P, const
         }
     }
     while (qn > 0) retry();
+    consume_count();
     if (MODE == MODE_GET && O.agg) {
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
@@ -508,11 +526,11 @@ __global__ void __launch_bounds__(256) kmers_kernel(const BriskParams P, const K
                 if (slots) slots[i] = found ? slot : ~0ull;
                 if (flags) flags[i] = found;
                 if (data) {
-                    if (T.data_size == 1) data[i] = found ? (unsigned char)(mt >> 24) : 0;
+                    if (T.data_size == 1) data[i] = found ? (unsigned char)mt : 0;
                     else for (u32 q = 0; q < T.data_size; q++) data[i * T.data_size + q] = found ? T.data[slot * T.data_size + q] : 0;
                 }
             } else {
-                const u32 add = MODE == MODE_COUNT ? META_COUNT_ONE : 0u;
+                const u32 add = MODE == MODE_COUNT ? 1u : 0u;
                 int res = store_upsert<KW>(T, lo, hi, idx, add, home, slot);
                 if (res == 1) {
                     new_keys++;
@@ -576,6 +594,7 @@ __global__ void __launch_bounds__(256) rehash_kernel(const BriskParams P, StoreV
             if (won) {
                 p->meta = v.meta;
                 p->aux = v.aux;
+                to.cnt[s] = from.cnt[i];
                 if (KW == 2) reinterpret_cast<u64 *>(p)[3] = reinterpret_cast<const u64 *>(&v)[3];
                 if (from.data) for (u32 q = 0; q < from.data_size; q++) to.data[s * to.data_size + q] = from.data[i * from.data_size + q];
                 break;
@@ -615,11 +634,45 @@ __global__ void __launch_bounds__(256) dump_kernel(StoreView T, KmerIn *keys, un
                 keys[o] = kk;
             }
             if (data) {
-                if (T.data_size == 1) data[o] = (unsigned char)(meta >> 24);
+                if (T.data_size == 1) data[o] = (unsigned char)T.cnt[i];
                 else for (u32 q = 0; q < T.data_size; q++) data[o * T.data_size + q] = T.data[i * T.data_size + q];
             }
         }
     }
+}
+
+// out[0] += sum of checksum_mix over the stored k-mers, out[1] += sum of their DATA bytes, out[2] += their number
+template <int KW>
+__global__ void __launch_bounds__(256) checksum_kernel(StoreView T, int n_special, u64 *out) {
+    typedef typename SlotOf<KW>::type S;
+    const S *tab = reinterpret_cast<const S *>(T.slots);
+    const u64 total = T.mask + 1 + (u64)n_special;
+    u64 a = 0, b = 0, c = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x) {
+        u64 lo, hi = 0;
+        u32 meta;
+        if (i <= T.mask) {
+            lo = *reinterpret_cast<const u64 *>(tab + i);
+            if (KW == 2) hi = reinterpret_cast<const u64 *>(tab + i)[1];
+            if (lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY)) continue;
+            meta = tab[i].meta;
+        } else {
+            meta = T.special[i - T.mask - 1];
+            if ((meta & META_TAG_MASK) == 0) continue;
+            lo = STORE_EMPTY;
+            hi = KW == 2 ? STORE_EMPTY : 0;
+        }
+        const u32 d = T.cnt[i] & 0xffu;
+        a += checksum_mix(lo, hi, (meta & META_TAG_MASK) - 1, d);
+        b += d;
+        c += 1;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, d);
+        b += __shfl_xor_sync(0xffffffffu, b, d);
+        c += __shfl_xor_sync(0xffffffffu, c, d);
+    }
+    if ((threadIdx.x & 31) == 0 && c) { atomicAdd(out, a); atomicAdd(out + 1, b); atomicAdd(out + 2, c); }
 }
 
 template <int KW>

@@ -69,3 +69,29 @@ def read_set(G, L, coverage, seed, max_reads=None):
     arr = reads(gen, L, seed, 0, n)
     offsets = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
     return arr.reshape(-1), offsets
+
+
+# ---- the same generator on the device (libbrisk_b200: brisk_synth_genome / brisk_synth_reads, csrc/synth.cuh)
+def device_genome(G, seed, device=None):
+    """torch uint8 tensor of G bases on the current CUDA device, bit-identical to genome(G, seed)"""
+    import torch
+    from . import _capi
+    lib = _capi.load()
+    out = torch.empty(G, dtype=torch.uint8, device=device or "cuda")
+    rc = lib.brisk_synth_genome(out.data_ptr(), G, seed, torch.cuda.current_stream().cuda_stream)
+    if rc:
+        raise RuntimeError(lib.brisk_last_error().decode())
+    return out
+
+
+def device_reads(gen, L, seed, first, count, out=None):
+    """torch uint8 tensor of count * L bases (reads first .. first+count-1), bit-identical to reads(...).reshape(-1)"""
+    import torch
+    from . import _capi
+    lib = _capi.load()
+    if out is None:
+        out = torch.empty(count * L, dtype=torch.uint8, device=gen.device)
+    rc = lib.brisk_synth_reads(gen.data_ptr(), gen.numel(), L, seed, first, count, out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    if rc:
+        raise RuntimeError(lib.brisk_last_error().decode())
+    return out

@@ -127,6 +127,18 @@ int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, u
 int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t *nb_kmers,
                 uint64_t *device_bytes, uint64_t *largest_bucket);
 
+/* order-independent checksum of the stored set held by this handle (its shard of a sharded index): out[0] = sum of a
+ * 64-bit mix of every stored (kmer_s, minimizer_idx, DATA byte), out[1] = sum of the DATA bytes, out[2] = number of
+ * stored k-mers.  The sums over the shards equal the sums of an unsharded index over the same reads. */
+int brisk_checksum(brisk_t *h, uint64_t out[3]);
+
+/* benchmark / test support: the synthetic generator of brisk_b200/synth.py on the device,
+ * bit-identical to it.  genome / out are device pointers on the current device, stream a cudaStream_t (NULL = default
+ * stream); the kernels are queued, not waited for.  Reads first .. first+count-1 of the set, L bytes each. */
+int brisk_synth_genome(void *genome, uint64_t G, uint64_t seed, void *stream);
+int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uint64_t seed, uint64_t first, uint64_t count, void *out,
+                      void *stream);
+
 /* grow the store so that n_keys distinct k-mers fit (the GPU analogue of Brisk::reallocate) */
 int brisk_reserve(brisk_t *h, uint64_t n_keys);
 int brisk_capacity(brisk_t *h, uint64_t *slots);

@@ -77,3 +77,43 @@ def test_hint_four_times_too_small_with_a_full_batch():
     lo, hi, ix, cnt = idx.dump()
     assert int(cnt.astype(np.int64).sum()) == 2 * occ
     assert idx.stats()["nb_kmers"] == len(lo) > 30_000_000
+
+
+def test_device_read_generator_is_bit_identical_to_the_host_generator():
+    """reads are generated on the device for the big configurations; same bytes as brisk_b200.synth."""
+    import torch
+    from brisk_b200 import synth
+    for (G, L, seed, first, count) in [(1_000_003, 150, 5, 0, 5000), (777_777, 250, 3, 123_456, 3001), (400, 150, 9, 7, 64)]:
+        gen_h = synth.genome(G, seed)
+        gen_d = synth.device_genome(G, seed)
+        assert np.array_equal(gen_d.cpu().numpy(), gen_h)
+        rd = synth.device_reads(gen_d, L, seed, first, count)
+        torch.cuda.synchronize()
+        assert np.array_equal(rd.cpu().numpy(), synth.reads(gen_h, L, seed, first, count).reshape(-1))
+
+
+def test_checksum_is_order_independent_and_additive_over_shards():
+    """brisk_checksum: the sums of two indexes over disjoint bucket sets add up to the sums of the index over everything
+    (what bench.py's parity_check relies on at N > 1), and equal the host-side sums of the dump."""
+    from brisk_b200 import Brisk, Parameters, synth
+    k, m, b, L = 63, 21, 14, 250
+    bases, offs = synth.read_set(300_000, L, 8, 17)
+    whole = Brisk(Parameters(k, m, b))
+    whole.count_reads(bases, offs)
+    cs = whole.checksum()
+    lo, hi, ix, cnt = whole.dump()
+    assert cs[2] == len(lo) == whole.stats()["nb_kmers"] and cs[1] == int(cnt.astype(np.int64).sum())
+    # two virtual ranks through the partition entry points
+    src = Brisk(Parameters(k, m, b))
+    recs, starts = src.partition_reads(bases, offs, 2)
+    parts = []
+    for r in range(2):
+        shard = Brisk(Parameters(k, m, b))
+        shard.apply_records(np.ascontiguousarray(recs[int(starts[r]):int(starts[r + 1])]), "count")
+        parts.append(shard.checksum())
+    M = (1 << 64) - 1
+    assert ((parts[0][0] + parts[1][0]) & M, parts[0][1] + parts[1][1], parts[0][2] + parts[1][2]) == cs
+    # a second pass over the same reads changes the counts, hence the mix sum, not the number of keys
+    whole.count_reads(bases, offs)
+    cs2 = whole.checksum()
+    assert cs2[2] == cs[2] and cs2[1] == 2 * cs[1] and cs2[0] != cs[0]
