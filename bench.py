@@ -230,7 +230,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from brisk_b200 import Brisk, Parameters, synth
-    from brisk_b200.brisk import F_GENERIC_ENUM, F_LITERAL_DECYCLE
+    from brisk_b200.brisk import F_GENERIC_ENUM, F_LITERAL_DECYCLE, F_SERIAL_EXCHANGE
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -266,7 +266,10 @@ def run_ours(args):
     offs_dev = offs_host.cuda()
     torch.cuda.synchronize()
 
+    base_flags = F_SERIAL_EXCHANGE if args.serial_exchange else 0
+
     def make_index(flags=0, sharded=True):
+        flags |= base_flags
         idx = Brisk(Parameters(K, M, B), capacity_hint=W.hint() if sharded else W.hint_total, device=local, flags=flags)
         idx.set_stream(stream.cuda_stream)
         if world > 1 and sharded:
@@ -475,6 +478,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="profiling runs: skip the CPU reference leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: skip the host-buffer arm")
     ap.add_argument("--no-parity", action="store_true", help="profiling runs: skip the independent index of the parity check")
+    ap.add_argument("--serial-exchange", action="store_true", help="experiments: N > 1 without the chunk-pipelined exchange")
     ap.add_argument("--hint-scale", type=float, default=1.0, help="experiments: multiply the capacity hint (table size)")
     ap.add_argument("--genome", type=int, default=0, help="profiling runs: smaller genome (the default is the config's)")
     args = ap.parse_args()

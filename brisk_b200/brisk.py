@@ -25,6 +25,7 @@ F_MANAGED = 1
 F_LITERAL_DECYCLE = 2
 F_SYNC_INSERT = 4
 F_GENERIC_ENUM = 8
+F_SERIAL_EXCHANGE = 16
 
 
 class BriskError(RuntimeError):

@@ -340,6 +340,12 @@ extern "C" int brisk_destroy(brisk_t *h) {
     for (DevBuf *b : bufs) b->release();
     if (h->comm) {
         if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
+        if (h->comm->stream) cudaStreamDestroy(h->comm->stream);
+        for (int i = 0; i < COMM_MAX_CHUNKS; i++) if (h->comm->ev_enum[i]) cudaEventDestroy(h->comm->ev_enum[i]);
+        if (h->comm->ev_counts) cudaEventDestroy(h->comm->ev_counts);
+        if (h->comm->ev_done) cudaEventDestroy(h->comm->ev_done);
+        if (h->comm->h_pinned) cudaFreeHost(h->comm->h_pinned);
+        cudaFree(h->comm->d_gather);
         delete h->comm;
     }
     cudaFree(h->d_part);
@@ -610,14 +616,15 @@ static u64 *part_matrix(brisk_handle *h) { return h->d_part + 64 + 65 + 64; }
 
 template <int RW>
 static cudaError_t launch_partition(brisk_handle *h, u64 *scratch, const u64 *recs, const u64 *occ, uint64_t n_recs, uint32_t n_dest, int mode,
-                                    u64 *dst, u64 *dst_occ) {
+                                    u64 *dst, u64 *dst_occ, cudaStream_t stream = nullptr) {
+    if (!stream) stream = h->stream;
     const int shift = 64 - 2 * h->P.b;
     u64 *totals = scratch, *starts = scratch + 64, *cursors = scratch + 64 + 65;
     unsigned b1 = (unsigned)std::min<uint64_t>((n_recs + PART_THREADS - 1) / PART_THREADS, 148 * 8);
-    partition_count_kernel<RW><<<b1, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_dest, mode, totals);
-    partition_starts_kernel<<<1, 32, 0, h->stream>>>(totals, n_dest, starts, cursors);
+    partition_count_kernel<RW><<<b1, PART_THREADS, 0, stream>>>(recs, n_recs, shift, n_dest, mode, totals);
+    partition_starts_kernel<<<1, 32, 0, stream>>>(totals, n_dest, starts, cursors);
     unsigned b2 = (unsigned)std::min<uint64_t>((n_recs + PART_TILE - 1) / PART_TILE, 148 * 8);
-    partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, h->stream>>>(recs, n_recs, shift, n_dest, mode, cursors, dst, occ, occ ? dst_occ : nullptr);
+    partition_scatter_kernel<RW><<<b2, PART_THREADS, 0, stream>>>(recs, n_recs, shift, n_dest, mode, cursors, dst, occ, occ ? dst_occ : nullptr);
     return cudaGetLastError();
 }
 
@@ -769,6 +776,136 @@ static int exchange_records(brisk_handle *h, uint64_t n_recs, bool with_occ, Exc
     return BRISK_OK;
 }
 
+// Pipelined form of enumerate + exchange for calls without per-occurrence outputs (the hot path: brisk_count_reads,
+// brisk_query_reads).  The batch is enumerated in chunks on the handle's stream; as soon as a chunk's records exist the
+// exchange stream partitions them by owner, all-gathers the per-destination totals (plus one status word per rank, so
+// that a rank-local failure is seen by everybody and all ranks leave the call together), and sends / receives them,
+// while the handle's stream is already enumerating the next chunk.  The host only waits on the exchange stream's small
+// count copies (pinned memory); the chunks shrink towards the end (40/30/20/10 %), so what stays exposed after the last
+// enumerate launch is the exchange of a tenth of the batch.
+// Returns BRISK_OK with X filled (records in d_recv), or 1 when the ranks agreed to fall back to the unpipelined path
+// (record buffer overflow somewhere), or an error every rank returns alike.
+static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_status, Exchange &X, uint64_t &n_recs_out) {
+    Comm &c = *h->comm;
+    const int RW = h->P.rec_words, n = c.n;
+    // chunk boundaries (reads): the host-input chunks as staged, or a geometric split of a device-resident batch
+    std::vector<uint64_t> cf;
+    if (B.chunk_events || B.n_reads < 65536) cf = B.chunk_first;
+    else {
+        // whole waves of the enumerate grid per chunk (8 CTAs of 128 reads per SM), shrinking towards the end:
+        // cuts after about 45 %, 75 % and all but the last wave
+        static int sms = 0;
+        if (!sms) { cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device); if (sms <= 0) sms = 148; }
+        const uint64_t wave = (uint64_t)sms * 8 * ENUM_THREADS;
+        const uint64_t T = (B.n_reads + wave - 1) / wave;
+        uint64_t cuts[3] = {(uint64_t)(0.45 * (double)T + 0.5), (uint64_t)(0.75 * (double)T + 0.5), T - 1};
+        cf.push_back(0);
+        for (int i = 0; i < 3; i++) {
+            const uint64_t r = std::min(cuts[i] * wave, B.n_reads);
+            if (r > cf.back() && r < B.n_reads) cf.push_back(r);
+        }
+        cf.push_back(B.n_reads);
+    }
+    const size_t nc = cf.size() - 1;
+    if (nc > COMM_MAX_CHUNKS) return 1;
+    const uint64_t upper = B.total_bytes;
+    const uint64_t cap = std::min(upper + 1, (uint64_t)(3.0 * (double)upper / (h->P.w + 1)) + B.n_reads + 4096);
+    CK(h->d_recs.ensure((cap + 1) * RW * sizeof(uint64_t)));
+    CK(h->d_send.ensure((cap + 1) * RW * sizeof(uint64_t)));
+    uint64_t recv_cap = cap + cap / 4 + 4096;
+    CK(h->d_recv.ensure(recv_cap * RW * sizeof(uint64_t)));
+    recv_cap = h->d_recv.cap / (RW * sizeof(uint64_t));
+    CK(cudaMemsetAsync(h->d_rec_count, 0, sizeof(uint64_t), h->stream));
+    EnumOut out;
+    out.recs = (u64 *)h->d_recs.p;
+    out.rec_cap = cap;
+    out.rec_count = (u64 *)h->d_rec_count;
+    out.rec_occ = nullptr;
+    out.kmer_base = nullptr;
+    for (size_t ci = 0; ci < nc; ci++) {
+        const uint64_t r0 = cf[ci], r1 = cf[ci + 1];
+        if (B.chunk_events) CK(cudaStreamWaitEvent(h->stream, h->chunk_ev[ci], 0));
+        if (r1 > r0) {
+            pack_reads_kernel<<<(unsigned)((r1 - r0 + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
+            CK(cudaGetLastError());
+            if (ci == 0) CK(cudaEventRecord(h->ev[1], h->stream));
+            CK(launch_enum(h, B, r0, r1, out));
+            h->last_launches += 2;
+        } else if (ci == 0) CK(cudaEventRecord(h->ev[1], h->stream));
+        CK(cudaMemcpyAsync(c.h_pinned + ci, h->d_rec_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaEventRecord(c.ev_enum[ci], h->stream));
+    }
+    CK(cudaEventRecord(h->ev[2], h->stream));
+    uint64_t done = 0, recv_total = 0;
+    u64 *g_mine = c.d_gather, *g_all = c.d_gather + 65;
+    uint64_t *h_all = c.h_pinned + 16;
+    int verdict = BRISK_OK;
+    for (size_t ci = 0; ci < nc; ci++) {
+        CK(cudaEventSynchronize(c.ev_enum[ci]));
+        const uint64_t after = c.h_pinned[ci];
+        int status = local_status;
+        if (after > cap) status = 1;  // record buffer overflow: everybody falls back to the unpipelined path
+        const uint64_t r0 = done, r1 = std::min(after, cap), cnt = r1 - r0;
+        done = r1;
+        CK(cudaStreamWaitEvent(c.stream, c.ev_enum[ci], 0));
+        CK(cudaMemsetAsync(h->d_part, 0, 64 * sizeof(uint64_t), c.stream));
+        if (cnt) {
+            const u64 *src = (const u64 *)h->d_recs.p + r0 * RW;
+            u64 *dst = (u64 *)h->d_send.p + r0 * RW;
+            CK(RW == 2 ? launch_partition<2>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
+                       : RW == 4 ? launch_partition<4>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
+                                 : launch_partition<6>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream));
+            h->last_launches += 3;
+        }
+        // this rank's row: n totals + the status word
+        CK(cudaMemcpyAsync(g_mine, part_totals(h), (size_t)n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c.stream));
+        const uint64_t st64 = (uint64_t)(int64_t)status;
+        CK(cudaMemcpyAsync(g_mine + n, &st64, sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream));
+        NCK(g_nccl.AllGather(g_mine, g_all, (size_t)n + 1, ncclUint64, c.comm, c.stream));
+        CK(cudaMemcpyAsync(h_all, g_all, (size_t)n * (n + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+        CK(cudaEventRecord(c.ev_counts, c.stream));
+        CK(cudaEventSynchronize(c.ev_counts));
+        c.h_matrix.assign((size_t)n * n, 0);
+        for (int s = 0; s < n; s++) {
+            for (int d = 0; d < n; d++) c.h_matrix[(size_t)s * n + d] = h_all[(size_t)s * (n + 1) + d];
+            const int64_t st = (int64_t)h_all[(size_t)s * (n + 1) + n];
+            if (st != 0 && verdict == BRISK_OK) verdict = (int)st;
+        }
+        if (verdict != BRISK_OK) break;  // every rank sees the same matrix: all leave here
+        c.send_start.assign(n + 1, 0);
+        c.recv_start.assign(n + 1, 0);
+        exchange_plan(c.h_matrix.data(), n, c.rank, c.send_start.data(), c.recv_start.data());
+        if (c.send_start[n] != cnt) return fail(BRISK_E_COMM, "partition lost records");
+        const uint64_t n_recv = c.recv_start[n];
+        if (recv_total + n_recv > recv_cap) {  // rare: the receive arena grows, keeping what has arrived
+            CK(cudaStreamSynchronize(c.stream));
+            DevBuf bigger;
+            CK(bigger.ensure((recv_total + n_recv) * 2 * RW * sizeof(uint64_t)));
+            CK(cudaMemcpy(bigger.p, h->d_recv.p, recv_total * RW * sizeof(uint64_t), cudaMemcpyDeviceToDevice));
+            h->d_recv.release();
+            h->d_recv = bigger;
+            recv_cap = h->d_recv.cap / (RW * sizeof(uint64_t));
+        }
+        NCK(g_nccl.GroupStart());
+        for (int p = 0; p < n; p++) {
+            const uint64_t sc = c.send_start[p + 1] - c.send_start[p], rc_ = c.recv_start[p + 1] - c.recv_start[p];
+            if (sc) NCK(g_nccl.Send((const u64 *)h->d_send.p + (r0 + c.send_start[p]) * RW, sc * RW, ncclUint64, p, c.comm, c.stream));
+            if (rc_) NCK(g_nccl.Recv((u64 *)h->d_recv.p + (recv_total + c.recv_start[p]) * RW, rc_ * RW, ncclUint64, p, c.comm, c.stream));
+        }
+        NCK(g_nccl.GroupEnd());
+        recv_total += n_recv;
+    }
+    CK(cudaEventRecord(c.ev_done, c.stream));
+    CK(cudaStreamWaitEvent(h->stream, c.ev_done, 0));
+    if (verdict == 1) return 1;
+    if (verdict != BRISK_OK) return fail(verdict, verdict == local_status ? g_err : std::string("another rank of the sharded index failed in this call (status ") +
+                                                                                        std::to_string(verdict) + ")");
+    n_recs_out = done;
+    X.recs = (const u64 *)h->d_recv.p;
+    X.n = recv_total;
+    return BRISK_OK;
+}
+
 // the way back of per-occurrence results: owner-side arrays (d_ret_*) -> source-side arrays in send order
 // (d_out_* are the caller-order staging buffers, so the send-order copies live in d_cnt-independent buffers)
 static int return_results(brisk_handle *h, const Exchange &X, uint64_t n_recs, bool want_slots, bool want_flags, bool want_data,
@@ -916,9 +1053,13 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     ReadBatch B;
     int rc = stage_reads(h, bases, offsets, n_reads, B);
     if (rc) return rc;
-    SETTLE_PENDING(h);  // after staging: this call's host->device copies run while the previous store kernel finishes
     const bool with_occ = slots || flags || data_out;
     const bool sharded = h->comm && h->comm->n > 1;
+    // after staging: this call's host->device copies run while the previous store kernel finishes.  On a sharded index a
+    // deferred failure (store full) must not make this rank leave before the collectives of the call: it is carried
+    // into the exchange, where every rank learns of it
+    const int settle_rc = settle_pending(h);
+    if (settle_rc && !sharded) return settle_rc;
     uint64_t n_recs = 0, n_occ = 0;
     OccOut O;
     O.rec_occ = nullptr; O.slots = nullptr; O.flags = nullptr; O.data = nullptr; O.agg = nullptr;
@@ -963,22 +1104,35 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     // first half of the chunks while the second half is on its way was measured too: the count call grows by what the
     // next call saves, 15.6 -> 16.9 ms per step: the step is bound by its kernels, not by the copies.)
     {
-        rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
-        if (rc) return rc;
-        CK(cudaEventRecord(h->ev[2], h->stream));
         Exchange X;
-        X.recs = (const u64 *)h->d_recs.p;
-        X.n = n_recs;
-        if (sharded) {
-            rc = exchange_records(h, n_recs, with_occ, X);
+        bool exchanged = false;
+        if (sharded && !with_occ && !(h->flags & BRISK_F_SERIAL_EXCHANGE)) {
+            rc = exchange_pipelined(h, B, settle_rc, X, n_recs);
+            if (rc < 0) return rc;
+            exchanged = rc == BRISK_OK;
+        } else if (settle_rc) {
+            return settle_rc;
+        }
+        if (!exchanged) {
+            rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
             if (rc) return rc;
+            CK(cudaEventRecord(h->ev[2], h->stream));
+            X.recs = (const u64 *)h->d_recs.p;
+            X.n = n_recs;
+            if (sharded) {
+                rc = exchange_records(h, n_recs, with_occ, X);
+                if (rc) return rc;
+            }
         }
         const u64 *tags = !with_occ ? nullptr : sharded ? (const u64 *)h->d_recv_occ.p : (const u64 *)h->d_rec_occ.p;
         rc = by_region(X.recs, tags, X.n, sharded ? h->d_recs : h->d_send, sharded ? h->d_rec_occ : h->d_send_occ);
         if (rc) return rc;
         CK(cudaEventRecord(h->ev[3], h->stream));
         if (mode != MODE_GET) {
-            rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes, with_occ);
+            // occurrences about to be inserted: this rank's own bytes, or (sharded) the received records times the
+            // k-mers per record of the batch this rank enumerated itself
+            const uint64_t per_rec = n_recs ? (B.total_bytes + n_recs - 1) / n_recs : (uint64_t)h->P.w;
+            rc = pregrow(h, sharded ? X.n * std::min<uint64_t>(per_rec, (uint64_t)h->P.w) : B.total_bytes, with_occ);
             if (rc) return rc;
         }
         rc = stage_outputs();
@@ -1629,6 +1783,12 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
         delete c;
         return fail(BRISK_E_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
     }
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < COMM_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&c->ev_enum[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+    CK(cudaMallocHost((void **)&c->h_pinned, (16 + 65 * 64) * sizeof(uint64_t)));
+    CK(cudaMalloc((void **)&c->d_gather, (65 + 64 * 65) * sizeof(uint64_t)));
     h->comm = c;
     return BRISK_OK;
 }

@@ -81,9 +81,12 @@ static inline void exchange_plan(const uint64_t *counts, int n, int rank, uint64
 struct Comm {
     ncclComm_t comm = nullptr;
     int rank = 0, n = 1;
-    u64 *d_totals = nullptr;   // [64] records per destination of the current batch
-    u64 *d_starts = nullptr;   // [65]
-    u64 *d_cursors = nullptr;  // [64]
-    u64 *d_matrix = nullptr;   // [64 * 64] all-gathered counts
+    // The exchange runs on its own stream: while the records of chunk c travel, the handle's stream enumerates chunk
+    // c + 1 (brisk_capi.cu: exchange_pipelined).  The host only ever waits on this stream's events.
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_enum[16] = {}, ev_counts = nullptr, ev_done = nullptr;
+    uint64_t *h_pinned = nullptr;  // pinned: [0, 16) record counters after every chunk, [16, 16 + 65 * 64) gathered totals + status
+    u64 *d_gather = nullptr;       // device: [65] this rank's totals + status, then [64][65] everybody's
     std::vector<uint64_t> h_matrix, send_start, recv_start;
 };
+#define COMM_MAX_CHUNKS 16

@@ -53,6 +53,9 @@ typedef struct brisk_handle brisk_t;
 #define BRISK_F_GENERIC_ENUM 8u     /* debug: enumerate with the run-time-(k, m) kernel even when a compiled-in
                                     * specialisation exists for the parameter set */
 
+#define BRISK_F_SERIAL_EXCHANGE 16u  /* debug: sharded index without the chunk-pipelined exchange (enumerate everything, then
+                                    * partition, exchange, store one after the other) */
+
 /* one k-mer as the reference's kmer_full carries it */
 typedef struct {
     uint64_t lo, hi;       /* kmer_s */

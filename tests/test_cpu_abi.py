@@ -82,4 +82,4 @@ def test_create_flags_match_the_header():
     text = open(os.path.join(os.path.dirname(__file__), "..", "include", "brisk_b200.h")).read()
     flags = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define BRISK_F_(\w+)\s+(\d+)u", text)}
     assert flags == {"MANAGED": B.F_MANAGED, "LITERAL_DECYCLE": B.F_LITERAL_DECYCLE, "SYNC_INSERT": B.F_SYNC_INSERT,
-                     "GENERIC_ENUM": B.F_GENERIC_ENUM}
+                     "GENERIC_ENUM": B.F_GENERIC_ENUM, "SERIAL_EXCHANGE": B.F_SERIAL_EXCHANGE}
