@@ -371,7 +371,9 @@ def run_ours(args):
                                      "unsharded index on rank 0 over all ranks' reads")
         parity["reference_checksum"] = "%016x" % rcs[0]
         parity["reference_nb_kmers"] = rcs[2]
-        wrap_free = W.cov * 3 < 250  # counts stay below the uint8 wrap: the sum of the counts is the occurrences
+        # while the read set is not walked more than once and the coverage is moderate the counts stay below the uint8
+        # wrap and their sum is the number of occurrences inserted (beyond that only the reference index can tell)
+        wrap_free = (steps + 1) * world * n_reads <= W.total_reads and W.cov <= 60
         parity["ok"] = bool(rcs[0] == mix_sum and rcs[2] == parity["nb_kmers"] == parity["nb_kmers_stats"] and
                             rcs[1] == parity["sum_counts"] and
                             (not wrap_free or parity["sum_counts"] == parity["occurrences_inserted"]) and

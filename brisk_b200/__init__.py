@@ -6,4 +6,5 @@ count over reads and k-mers, dump, stats), plus the synthetic read generator of 
 Nothing here computes on the CPU: every call goes through the C ABI and fails loudly when the CUDA
 library is missing.
 """
-from .brisk import Brisk, BriskError, Parameters, decode_records, exchange_plan, lib_path, owner_of_bucket  # noqa: F401
+from .brisk import (Brisk, BriskError, Parameters, bucket_ids, decode_records, exchange_plan, lib_path,  # noqa: F401
+                    merge_ordered_dumps, owner_of_bucket)

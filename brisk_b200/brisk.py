@@ -130,6 +130,12 @@ class Brisk:
         order = np.argsort(occ >> np.uint64(1), kind="stable")
         return recs[order], occ[order]
 
+    def write_kff(self, path):
+        """BriskWriter::write: this handle's stored set as a KFF file; returns (blocks, minimizer sections) written."""
+        nb, ns = C.c_uint64(), C.c_uint64()
+        self._check(self._lib.brisk_write_kff(self._h, str(path).encode(), C.byref(nb), C.byref(ns)))
+        return nb.value, ns.value
+
     def checksum(self):
         """(sum of a 64-bit mix of every stored (kmer_s, minimizer_idx, DATA byte), sum of the DATA bytes, number of stored
         k-mers) of this handle's shard; order-independent, the shards' sums add up to the unsharded index's."""
@@ -321,6 +327,39 @@ def exchange_plan(counts, rank):
     if rc:
         raise BriskError("brisk_exchange_plan: %d" % rc)
     return ss, rs
+
+
+def bucket_ids(params, lo, hi, idx):
+    """bucket id of every (kmer_s, minimizer_idx): the middle 2b bits of the hashed m-mer found at minimizer_idx
+    (brisk/Brisk.hpp:135-137 after hash_kmer_minimizer_inplace; the integer rounds of brisk/hashing.cpp:10-16).  Host-side
+    helper for merging the ordered dumps of the shards of a sharded index; numpy, no device."""
+    k, m, b = params.k, params.m, params.b
+    M64 = (1 << 64) - 1
+    mask = (1 << (2 * m)) - 1
+    out = np.zeros(len(lo), np.uint64)
+    s = (m - b + 1) // 2
+    for i in range(len(lo)):
+        v = (int(hi[i]) << 64) | int(lo[i])
+        key = (v >> (2 * int(idx[i]))) & mask
+        key = ((~key & M64) + (key << 21)) & M64 & mask
+        key ^= key >> 24
+        key = ((key + (key << 3)) + (key << 8)) & M64 & mask
+        key ^= key >> 14
+        key = ((key + (key << 2)) + (key << 4)) & M64 & mask
+        key ^= key >> 28
+        key = (key + (key << 31)) & M64 & mask
+        out[i] = (key >> (2 * s)) & ((1 << (2 * b)) - 1)
+    return out
+
+
+def merge_ordered_dumps(params, parts):
+    """The ordered dumps (lo, hi, idx, data) of the shards of a sharded index merged into the order brisk_dump_ordered
+    gives for an unsharded index: increasing bucket id (DenseMenuYo::next, brisk/DenseMenuYo.hpp:476-521), then
+    (minimizer_idx, kmer_s).  Buckets are disjoint over the shards but interleaved (the owner of a bucket is a scramble
+    of its id), so the concatenation in rank order is not in bucket order: this is the k-way merge."""
+    lo, hi, ix, dat = (np.concatenate([p[i] for p in parts]) for i in range(4))
+    order = np.lexsort((lo, hi, ix, bucket_ids(params, lo, hi, ix)))
+    return lo[order], hi[order], ix[order], dat[order]
 
 
 def decode_records(recs, params):

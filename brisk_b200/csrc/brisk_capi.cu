@@ -9,7 +9,6 @@
 #include <string>
 #include <vector>
 
-#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/brisk_b200.h"
@@ -18,6 +17,8 @@
 #include "partition.cuh"
 #include "fasta.cuh"
 #include "store.cuh"
+#include "sort.cuh"
+#include "kff.cuh"
 #include "comm.cuh"
 
 static thread_local std::string g_err;
@@ -793,21 +794,22 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
     if (B.chunk_events || B.n_reads < 65536) cf = B.chunk_first;
     else {
         // whole waves of the enumerate grid per chunk (8 CTAs of 128 reads per SM), shrinking towards the end:
-        // cuts after about 45 %, 75 % and all but the last wave
+        // cuts after about 55 % and all but the last wave (every exchange costs a few hundred microseconds of latency
+        // whatever its size: few chunks)
         static int sms = 0;
         if (!sms) { cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device); if (sms <= 0) sms = 148; }
         const uint64_t wave = (uint64_t)sms * 8 * ENUM_THREADS;
         const uint64_t T = (B.n_reads + wave - 1) / wave;
-        uint64_t cuts[3] = {(uint64_t)(0.45 * (double)T + 0.5), (uint64_t)(0.75 * (double)T + 0.5), T - 1};
+        uint64_t cuts[2] = {(uint64_t)(0.55 * (double)T + 0.5), T - 1};
         cf.push_back(0);
-        for (int i = 0; i < 3; i++) {
+        for (int i = 0; i < 2; i++) {
             const uint64_t r = std::min(cuts[i] * wave, B.n_reads);
             if (r > cf.back() && r < B.n_reads) cf.push_back(r);
         }
         cf.push_back(B.n_reads);
     }
     const size_t nc = cf.size() - 1;
-    if (nc > COMM_MAX_CHUNKS) return 1;
+    if (nc > COMM_MAX_CHUNKS || n >= 64) return 1;  // (word n of the partition scratch carries the status: n < 64)
     const uint64_t upper = B.total_bytes;
     const uint64_t cap = std::min(upper + 1, (uint64_t)(3.0 * (double)upper / (h->P.w + 1)) + B.n_reads + 4096);
     CK(h->d_recs.ensure((cap + 1) * RW * sizeof(uint64_t)));
@@ -837,7 +839,7 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
     }
     CK(cudaEventRecord(h->ev[2], h->stream));
     uint64_t done = 0, recv_total = 0;
-    u64 *g_mine = c.d_gather, *g_all = c.d_gather + 65;
+    u64 *g_mine = c.d_gather, *g_all = c.d_gather + (64 + 65 + 64 + 8);
     uint64_t *h_all = c.h_pinned + 16;
     int verdict = BRISK_OK;
     for (size_t ci = 0; ci < nc; ci++) {
@@ -848,19 +850,20 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
         const uint64_t r0 = done, r1 = std::min(after, cap), cnt = r1 - r0;
         done = r1;
         CK(cudaStreamWaitEvent(c.stream, c.ev_enum[ci], 0));
-        CK(cudaMemsetAsync(h->d_part, 0, 64 * sizeof(uint64_t), c.stream));
+        // this rank's row of the gather = the partition's own totals (n words) followed by the status word
+        CK(cudaMemsetAsync(g_mine, 0, 65 * sizeof(uint64_t), c.stream));
+        if (status) {
+            const uint64_t st64 = (uint64_t)(int64_t)status;
+            CK(cudaMemcpyAsync(g_mine + n, &st64, sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream));
+        }
         if (cnt) {
             const u64 *src = (const u64 *)h->d_recs.p + r0 * RW;
             u64 *dst = (u64 *)h->d_send.p + r0 * RW;
-            CK(RW == 2 ? launch_partition<2>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
-                       : RW == 4 ? launch_partition<4>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
-                                 : launch_partition<6>(h, h->d_part, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream));
+            CK(RW == 2 ? launch_partition<2>(h, g_mine, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
+                       : RW == 4 ? launch_partition<4>(h, g_mine, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream)
+                                 : launch_partition<6>(h, g_mine, src, nullptr, cnt, (uint32_t)n, 0, dst, nullptr, c.stream));
             h->last_launches += 3;
         }
-        // this rank's row: n totals + the status word
-        CK(cudaMemcpyAsync(g_mine, part_totals(h), (size_t)n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c.stream));
-        const uint64_t st64 = (uint64_t)(int64_t)status;
-        CK(cudaMemcpyAsync(g_mine + n, &st64, sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream));
         NCK(g_nccl.AllGather(g_mine, g_all, (size_t)n + 1, ncclUint64, c.comm, c.stream));
         CK(cudaMemcpyAsync(h_all, g_all, (size_t)n * (n + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
         CK(cudaEventRecord(c.ev_counts, c.stream));
@@ -1364,28 +1367,123 @@ extern "C" int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap
 // ---- ordered dump: the stored set in the order DenseMenuYo::next walks it at bucket level
 // (increasing bucket id, brisk/DenseMenuYo.hpp:476-521); inside a bucket the reference's order is its arena's insertion
 // order, here (minimizer_idx, kmer_s) ascending so that the result is deterministic.
-__global__ void __launch_bounds__(256) dump_sortkeys_kernel(const BriskParams P, const KmerIn *__restrict__ keys, u64 n, u64 *lo, u64 *hi,
-                                                            u64 *top, u32 *perm) {
+// The sort permutes SLOT INDICES (u32) with our own LSD radix sort (sort.cuh); the key words are read from the table
+// through the permutation, so the temporaries are two u32 permutations (8 bytes per stored k-mer) + the histograms.
+template <int KW>
+__global__ void __launch_bounds__(256) dump_slots_kernel(StoreView T, int n_special, u32 *slots_out, u64 cap_out) {
+    typedef typename SlotOf<KW>::type S;
+    const S *tab = reinterpret_cast<const S *>(T.slots);
+    const u64 total = T.mask + 1 + (u64)n_special;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x) {
+        bool used;
+        if (i <= T.mask) {
+            const u64 lo = *reinterpret_cast<const u64 *>(tab + i);
+            const u64 hi = KW == 2 ? reinterpret_cast<const u64 *>(tab + i)[1] : 0;
+            used = !(lo == STORE_EMPTY && (KW == 1 || hi == STORE_EMPTY));
+        } else {
+            used = (T.special[i - T.mask - 1] & META_TAG_MASK) != 0;
+        }
+        if (used) {
+            const u64 o = atomicAdd(T.counters + 3, 1ull);
+            if (o < cap_out) slots_out[o] = (u32)i;
+        }
+    }
+}
+// key words of the k-mer stored in a slot (a special slot holds the all-ones key)
+template <int KW>
+struct SlotKey {
+    StoreView T;
+    BriskParams P;
+    __device__ __forceinline__ void load(u32 slot, u64 &lo, u64 &hi, u32 &idx) const {
+        typedef typename SlotOf<KW>::type S;
+        if (slot <= T.mask) {
+            const S *p = reinterpret_cast<const S *>(T.slots) + slot;
+            lo = *reinterpret_cast<const u64 *>(p);
+            hi = KW == 2 ? reinterpret_cast<const u64 *>(p)[1] : 0;
+            idx = (p->meta & META_TAG_MASK) - 1;
+        } else {
+            lo = STORE_EMPTY;
+            hi = KW == 2 ? STORE_EMPTY : 0;
+            idx = (T.special[slot - T.mask - 1] & META_TAG_MASK) - 1;
+        }
+    }
+};
+template <int KW> struct KeyLo : SlotKey<KW> {
+    __device__ __forceinline__ u64 operator()(u32 slot) const { u64 lo, hi; u32 idx; this->load(slot, lo, hi, idx); return lo; }
+};
+template <int KW> struct KeyHi : SlotKey<KW> {
+    __device__ __forceinline__ u64 operator()(u32 slot) const { u64 lo, hi; u32 idx; this->load(slot, lo, hi, idx); return hi; }
+};
+template <int KW> struct KeyBucketIdx : SlotKey<KW> {  // (bucket id << 8) | minimizer_idx
+    __device__ __forceinline__ u64 operator()(u32 slot) const {
+        u64 lo, hi; u32 idx;
+        this->load(slot, lo, hi, idx);
+        return (bucket_of_kmer(this->P, lo, hi, (int)idx) << 8) | idx;
+    }
+};
+template <int KW>
+__global__ void __launch_bounds__(256) gather_slots_kernel(SlotKey<KW> K, const u32 *__restrict__ perm, u64 n, KmerIn *okeys, unsigned char *odata) {
     u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const KmerIn k = keys[i];
-    lo[i] = k.lo;
-    hi[i] = k.hi;
-    top[i] = (bucket_of_kmer(P, k.lo, k.hi, (int)k.idx) << 8) | k.idx;
-    perm[i] = (u32)i;
+    const u32 slot = perm[i];
+    u64 lo, hi; u32 idx;
+    K.load(slot, lo, hi, idx);
+    if (okeys) {
+        KmerIn kk;
+        kk.lo = lo; kk.hi = hi; kk.idx = (unsigned char)idx;
+        for (int q = 0; q < 7; q++) kk.pad[q] = 0;
+        okeys[i] = kk;
+    }
+    if (odata) {
+        if (K.T.data_size == 1) odata[i] = (unsigned char)K.T.cnt[slot];
+        else for (u32 q = 0; q < K.T.data_size; q++) odata[i * K.T.data_size + q] = K.T.data[(u64)slot * K.T.data_size + q];
+    }
 }
-__global__ void __launch_bounds__(256) gather64_kernel(const u64 *__restrict__ src, const u32 *__restrict__ perm, u64 n, u64 *dst) {
-    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = src[perm[i]];
-}
-__global__ void __launch_bounds__(256) gather_dump_kernel(const KmerIn *__restrict__ keys, const unsigned char *__restrict__ data,
-                                                          u32 data_size, const u32 *__restrict__ perm, u64 n, KmerIn *okeys,
-                                                          unsigned char *odata) {
+// the largest number of k-mers one bucket holds, from the slots sorted by bucket id: every run start walks its run
+template <int KW>
+__global__ void __launch_bounds__(256) bucket_runs_kernel(KeyBucketIdx<KW> K, const u32 *__restrict__ perm, u64 n, u64 *out_max) {
     u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const u32 s = perm[i];
-    if (okeys) okeys[i] = keys[s];
-    if (odata) for (u32 q = 0; q < data_size; q++) odata[i * data_size + q] = data[(u64)s * data_size + q];
+    const u64 b = K(perm[i]) >> 8;
+    if (i > 0 && (K(perm[i - 1]) >> 8) == b) return;
+    u64 len = 1;
+    while (i + len < n && (K(perm[i + len]) >> 8) == b) len++;
+    atomicMax(out_max, len);
+}
+
+// slots of the stored k-mers sorted by (bucket id[, minimizer_idx, kmer_s]); *result points into perm_a / perm_b
+template <int KW>
+static int sorted_slots_t(brisk_handle *h, uint64_t nk, bool full_order, DevBuf &perm_a, DevBuf &perm_b, DevBuf &hist, u32 **result) {
+    CK(perm_a.ensure((nk + 1) * sizeof(u32)));
+    CK(perm_b.ensure((nk + 1) * sizeof(u32)));
+    CK(hist.ensure(radix_sort_hist_bytes(nk) + 1024));
+    CK(cudaMemsetAsync(h->counters + 3, 0, sizeof(uint64_t), h->stream));
+    unsigned blocks = (unsigned)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
+    dump_slots_kernel<KW><<<blocks, 256, 0, h->stream>>>(view_of(h), 64, (u32 *)perm_a.p, nk);
+    CK(cudaGetLastError());
+    uint64_t got = 0;
+    CK(cudaMemcpyAsync(&got, h->counters + 3, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (got != nk) return fail(BRISK_E_CUDA, "dump found " + std::to_string(got) + " keys, expected " + std::to_string(nk));
+    u32 *cur = (u32 *)perm_a.p, *other = (u32 *)perm_b.p;
+    auto swap_to = [&](u32 *res) { if (res != cur) { other = cur; cur = res; } };
+    u32 *res = cur;
+    if (full_order) {
+        // least-significant first: kmer_s low word, high word, then (bucket id, minimizer_idx); every pass is stable
+        KeyLo<KW> klo; klo.T = view_of(h); klo.P = h->P;
+        CK(radix_sort_perm(klo, cur, other, nk, 0, std::min(64, 2 * h->P.k), (u32 *)hist.p, h->stream, &res));
+        swap_to(res);
+        if (KW == 2) {
+            KeyHi<KW> khi; khi.T = view_of(h); khi.P = h->P;
+            CK(radix_sort_perm(khi, cur, other, nk, 0, 2 * h->P.k - 64, (u32 *)hist.p, h->stream, &res));
+            swap_to(res);
+        }
+    }
+    KeyBucketIdx<KW> kb; kb.T = view_of(h); kb.P = h->P;
+    CK(radix_sort_perm(kb, cur, other, nk, full_order ? 0 : 8, 2 * h->P.b + 8, (u32 *)hist.p, h->stream, &res));
+    swap_to(res);
+    *result = cur;
+    return BRISK_OK;
 }
 
 extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n) {
@@ -1396,45 +1494,25 @@ extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint
     if (n) *n = nk;
     if (!keys && !data) return BRISK_OK;
     if (cap < nk) return fail(BRISK_E_CAPACITY, "dump buffers too small");
-    if (nk >= (1ull << 32)) return fail(BRISK_E_CAPACITY, "ordered dump handles fewer than 2^32 k-mers per shard");
+    if (h->cap + 64 > (1ull << 32)) return fail(BRISK_E_CAPACITY, "ordered dump handles tables of fewer than 2^32 slots per shard");
     if (nk == 0) return BRISK_OK;
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     SETTLE_PENDING(h);
-    DevBuf ukeys, udata, lo, hi, top, tmpk, perm, perm2, cubtmp, okeys, odata;
-    auto cleanup = [&]() { for (DevBuf *b : {&ukeys, &udata, &lo, &hi, &top, &tmpk, &perm, &perm2, &cubtmp, &okeys, &odata}) b->release(); };
+    DevBuf perm_a, perm_b, hist, okeys, odata;
+    auto cleanup = [&]() { for (DevBuf *b : {&perm_a, &perm_b, &hist, &okeys, &odata}) b->release(); };
     auto body = [&]() -> int {
-        CK(ukeys.ensure(nk * sizeof(KmerIn)));
-        CK(udata.ensure(nk * h->data_size));
-        int r = brisk_dump(h, (brisk_kmer *)ukeys.p, udata.p, nk, &nk);  // unordered, device to device
+        u32 *perm = nullptr;
+        int r = h->P.key_words == 1 ? sorted_slots_t<1>(h, nk, true, perm_a, perm_b, hist, &perm) : sorted_slots_t<2>(h, nk, true, perm_a, perm_b, hist, &perm);
         if (r) return r;
-        std::lock_guard<std::recursive_mutex> lock(h->mu);
-        for (DevBuf *b : {&lo, &hi, &top, &tmpk}) CK(b->ensure(nk * sizeof(u64)));
-        CK(perm.ensure(nk * sizeof(u32)));
-        CK(perm2.ensure(nk * sizeof(u32)));
-        const unsigned blocks = (unsigned)((nk + 255) / 256);
-        dump_sortkeys_kernel<<<blocks, 256, 0, h->stream>>>(h->P, (const KmerIn *)ukeys.p, nk, (u64 *)lo.p, (u64 *)hi.p, (u64 *)top.p, (u32 *)perm.p);
-        CK(cudaGetLastError());
-        size_t tb = 0;
-        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, (u64 *)lo.p, (u64 *)tmpk.p, (u32 *)perm.p, (u32 *)perm2.p, (int)nk, 0, 64, h->stream));
-        CK(cubtmp.ensure(tb));
-        // least-significant first: kmer_s low word, high word, then (bucket id, minimizer_idx); every pass is stable
-        u32 *pa = (u32 *)perm.p, *pb = (u32 *)perm2.p;
-        CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 64, h->stream));
-        std::swap(pa, pb);
-        if (h->P.key_words == 2) {
-            gather64_kernel<<<blocks, 256, 0, h->stream>>>((const u64 *)hi.p, pa, nk, (u64 *)lo.p);
-            CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 2 * h->P.k - 64, h->stream));
-            std::swap(pa, pb);
-        }
-        gather64_kernel<<<blocks, 256, 0, h->stream>>>((const u64 *)top.p, pa, nk, (u64 *)lo.p);
-        CK(cub::DeviceRadixSort::SortPairs(cubtmp.p, tb, (u64 *)lo.p, (u64 *)tmpk.p, pa, pb, (int)nk, 0, 2 * h->P.b + 8, h->stream));
-        std::swap(pa, pb);
         const bool k_dev = is_device_ptr(keys), d_dev = is_device_ptr(data);
         KmerIn *ok = nullptr;
         unsigned char *od = nullptr;
         if (keys) { if (k_dev) ok = (KmerIn *)keys; else { CK(okeys.ensure(nk * sizeof(KmerIn))); ok = (KmerIn *)okeys.p; } }
         if (data) { if (d_dev) od = (unsigned char *)data; else { CK(odata.ensure(nk * h->data_size)); od = (unsigned char *)odata.p; } }
-        gather_dump_kernel<<<blocks, 256, 0, h->stream>>>((const KmerIn *)ukeys.p, (const unsigned char *)udata.p, h->data_size, pa, nk, ok, od);
+        const unsigned blocks = (unsigned)((nk + 255) / 256);
+        if (h->P.key_words == 1) { SlotKey<1> K; K.T = view_of(h); K.P = h->P; gather_slots_kernel<1><<<blocks, 256, 0, h->stream>>>(K, perm, nk, ok, od); }
+        else { SlotKey<2> K; K.T = view_of(h); K.P = h->P; gather_slots_kernel<2><<<blocks, 256, 0, h->stream>>>(K, perm, nk, ok, od); }
         CK(cudaGetLastError());
         if (keys && !k_dev) CK(cudaMemcpyAsync(keys, ok, nk * sizeof(KmerIn), cudaMemcpyDeviceToHost, h->stream));
         if (data && !d_dev) CK(cudaMemcpyAsync(data, od, nk * h->data_size, cudaMemcpyDeviceToHost, h->stream));
@@ -1443,6 +1521,174 @@ extern "C" int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint
     };
     rc = body();
     cleanup();
+    return rc;
+}
+
+// the largest number of k-mers stored under one bucket id (the reference's `largest_bucket` counts the SKL records of a
+// bucket, which depends on its insertion order, brisk/DenseMenuYo.hpp:262-264; this is the order-independent analogue)
+static int largest_bucket_kmers(brisk_handle *h, uint64_t &out) {
+    out = 0;
+    const uint64_t nk = h->n_keys;
+    if (nk == 0 || h->cap + 64 > (1ull << 32)) return BRISK_OK;
+    DevBuf perm_a, perm_b, hist;
+    auto body = [&]() -> int {
+        u32 *perm = nullptr;
+        int r = h->P.key_words == 1 ? sorted_slots_t<1>(h, nk, false, perm_a, perm_b, hist, &perm) : sorted_slots_t<2>(h, nk, false, perm_a, perm_b, hist, &perm);
+        if (r) return r;
+        CK(cudaMemsetAsync(h->counters + 4, 0, sizeof(uint64_t), h->stream));
+        const unsigned blocks = (unsigned)((nk + 255) / 256);
+        if (h->P.key_words == 1) { KeyBucketIdx<1> K; K.T = view_of(h); K.P = h->P; bucket_runs_kernel<1><<<blocks, 256, 0, h->stream>>>(K, perm, nk, h->counters + 4); }
+        else { KeyBucketIdx<2> K; K.T = view_of(h); K.P = h->P; bucket_runs_kernel<2><<<blocks, 256, 0, h->stream>>>(K, perm, nk, h->counters + 4); }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&out, h->counters + 4, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        return BRISK_OK;
+    };
+    int rc = body();
+    for (DevBuf *b : {&perm_a, &perm_b, &hist}) b->release();
+    return rc;
+}
+
+// ---- KFF writer: BriskWriter::write (brisk/writer.hpp:75-179) for this handle's shard
+static void kff_be(std::vector<unsigned char> &v, int bytes, uint64_t x) {
+    for (int i = bytes - 1; i >= 0; i--) v.push_back((unsigned char)(x >> (8 * i)));
+}
+static void kff_gv_section(std::vector<unsigned char> &v, const std::vector<std::pair<std::string, uint64_t>> &vars) {
+    // Section_GV::close (brisk/lib/kff/kff_io.cpp:786-803): 'v', number of variables, then name\0 + value in the order of
+    // the std::map it keeps them in (callers pass them sorted by name)
+    v.push_back('v');
+    kff_be(v, 8, vars.size());
+    for (auto &kv : vars) {
+        for (char ch : kv.first) v.push_back((unsigned char)ch);
+        v.push_back(0);
+        kff_be(v, 8, kv.second);
+    }
+}
+static int ceil_log2_u64(uint64_t x) {  // ceil(log2(x)) as the KFF library computes field widths (kff_io.cpp:1063-1069)
+    int b = 0;
+    while (((uint64_t)1 << b) < x) b++;
+    return b;
+}
+
+template <int KW>
+static int write_kff_t(brisk_handle *h, FILE *f, uint64_t &n_blocks, uint64_t &n_sections) {
+    const BriskParams &P = h->P;
+    KffGeom G;
+    G.k = P.k; G.m = P.m; G.data_size = (int)h->data_size;
+    const uint64_t kff_max = 2 * (uint64_t)(P.k - P.m);  // writer.hpp:92
+    G.nb_kmers_bytes = (ceil_log2_u64(kff_max) + 7) / 8;
+    G.mini_pos_bytes = (ceil_log2_u64((uint64_t)P.k + kff_max - 1) + 7) / 8;
+    G.mini_bytes = (P.m + 3) / 4;
+    // file header (Kff_file::open 'w', write_encoding(0, 1, 3, 2), write_metadata: writer.hpp:23-31)
+    std::vector<unsigned char> head = {'K', 'F', 'F', 1, 0, (unsigned char)((0 << 6) | (1 << 4) | (3 << 2) | 2), 0, 0};
+    const std::string meta = "File generated with Brisk v1. See https://github.com/Malfoy/Brisk";
+    kff_be(head, 4, meta.size());
+    head.insert(head.end(), meta.begin(), meta.end());
+    std::vector<std::pair<uint64_t, char>> sections;  // absolute position, type
+    sections.push_back({head.size(), 'v'});
+    kff_gv_section(head, {{"data_size", h->data_size}, {"k", (uint64_t)P.k}, {"max", 1}});            // writer.hpp:78-82
+    sections.push_back({head.size(), 'v'});
+    kff_gv_section(head, {{"data_size", h->data_size}, {"k", (uint64_t)P.k}, {"m", (uint64_t)P.m}, {"max", kff_max}});  // :86-91
+    const uint64_t body0 = head.size();
+
+    const uint64_t nk = h->n_keys;
+    DevBuf link, chains, perm_a, perm_b, hist, sizes, first, offs, ords, scan_tmp, body, secpos;
+    auto cleanup = [&]() { for (DevBuf *b : {&link, &chains, &perm_a, &perm_b, &hist, &sizes, &first, &offs, &ords, &scan_tmp, &body, &secpos}) b->release(); };
+    std::vector<unsigned char> h_body;
+    std::vector<uint64_t> h_secpos;
+    uint64_t n_chains = 0, body_bytes = 0;
+    auto device_part = [&]() -> int {
+        if (nk == 0) return BRISK_OK;
+        if (h->cap >= (1ull << 40)) return fail(BRISK_E_CAPACITY, "KFF writer handles tables of fewer than 2^40 slots");
+        StoreView T = view_of(h);
+        CK(link.ensure((h->cap + 1) * sizeof(u64)));
+        CK(chains.ensure((nk + 1) * sizeof(KffChain)));
+        const unsigned blocks = (unsigned)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
+        kff_links_kernel<KW><<<blocks, 256, 0, h->stream>>>(P, T, (u64 *)link.p);
+        kff_edges_kernel<<<blocks, 256, 0, h->stream>>>((u64 *)link.p, h->cap);
+        CK(cudaMemsetAsync(h->counters + 3, 0, sizeof(uint64_t), h->stream));
+        kff_chains_kernel<KW><<<blocks, 256, 0, h->stream>>>(P, T, (const u64 *)link.p, 64, (KffChain *)chains.p, nk, h->counters + 3);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&n_chains, h->counters + 3, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        if (n_chains == 0 || n_chains > nk) return fail(BRISK_E_CUDA, "KFF writer: inconsistent chain count");
+        if (n_chains >= (1ull << 32)) return fail(BRISK_E_CAPACITY, "KFF writer handles fewer than 2^32 superkmers per shard");
+        // order the chains by bucket id, then minimizer
+        CK(perm_a.ensure(n_chains * sizeof(u32)));
+        CK(perm_b.ensure(n_chains * sizeof(u32)));
+        CK(hist.ensure(radix_sort_hist_bytes(n_chains) + 1024));
+        const unsigned cb = (unsigned)((n_chains + 255) / 256);
+        sort_iota_kernel<<<cb, 256, 0, h->stream>>>((u32 *)perm_a.p, n_chains);
+        KffChainKey ck; ck.chains = (const KffChain *)chains.p;
+        u32 *perm = nullptr;
+        CK(radix_sort_perm(ck, (u32 *)perm_a.p, (u32 *)perm_b.p, n_chains, 0, 2 * P.m, (u32 *)hist.p, h->stream, &perm));
+        // layout: bytes of every chain (+ section header where a section opens), section ordinals
+        for (DevBuf *b : {&sizes, &first, &offs, &ords}) CK(b->ensure((n_chains + 1) * sizeof(u64)));
+        kff_sizes_kernel<<<cb, 256, 0, h->stream>>>(G, (const KffChain *)chains.p, perm, n_chains, (u64 *)sizes.p, (u64 *)first.p);
+        CK(cudaMemsetAsync((u64 *)sizes.p + n_chains, 0, sizeof(u64), h->stream));
+        CK(cudaMemsetAsync((u64 *)first.p + n_chains, 0, sizeof(u64), h->stream));
+        size_t tmp = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, (u64 *)sizes.p, (u64 *)offs.p, (int)(n_chains + 1), h->stream));
+        CK(scan_tmp.ensure(tmp));
+        CK(cub::DeviceScan::ExclusiveSum(scan_tmp.p, tmp, (u64 *)sizes.p, (u64 *)offs.p, (int)(n_chains + 1), h->stream));
+        CK(cub::DeviceScan::ExclusiveSum(scan_tmp.p, tmp, (u64 *)first.p, (u64 *)ords.p, (int)(n_chains + 1), h->stream));
+        uint64_t tot[2] = {0, 0};
+        CK(cudaMemcpyAsync(&tot[0], (u64 *)offs.p + n_chains, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(&tot[1], (u64 *)ords.p + n_chains, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        body_bytes = tot[0];
+        n_sections = tot[1];
+        CK(body.ensure(body_bytes + 16));
+        CK(secpos.ensure((n_sections + 1) * sizeof(u64)));
+        kff_emit_kernel<KW><<<(unsigned)((n_chains + 127) / 128), 128, 0, h->stream>>>(P, G, T, (const u64 *)link.p, (const KffChain *)chains.p, perm,
+                                                                                       n_chains, (const u64 *)offs.p, (const u64 *)ords.p,
+                                                                                       (unsigned char *)body.p, (u64 *)secpos.p);
+        CK(cudaGetLastError());
+        h_body.resize(body_bytes);
+        h_secpos.resize(n_sections);
+        CK(cudaMemcpyAsync(h_body.data(), body.p, body_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(h_secpos.data(), secpos.p, n_sections * sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        return BRISK_OK;
+    };
+    int rc = device_part();
+    cleanup();
+    if (rc) return rc;
+    n_blocks = n_chains;
+    for (uint64_t p : h_secpos) sections.push_back({body0 + p, 'm'});
+    // footer (Kff_file::write_footer, kff_io.cpp:550-568): the index of every section, positions relative to the end of
+    // the index section, then a value section naming it, then the closing signature
+    std::vector<unsigned char> tail;
+    const uint64_t index_begin = body0 + body_bytes;
+    const int64_t index_end = (int64_t)(index_begin + 17 + 9 * sections.size());
+    tail.push_back('i');
+    kff_be(tail, 8, sections.size());
+    for (auto &sp : sections) {
+        tail.push_back((unsigned char)sp.second);
+        kff_be(tail, 8, (uint64_t)((int64_t)sp.first - index_end));
+    }
+    kff_be(tail, 8, 0);  // next_index
+    kff_gv_section(tail, {{"first_index", index_begin}, {"footer_size", 9 + 2 * (12 + 8)}});
+    tail.push_back('K'); tail.push_back('F'); tail.push_back('F');
+    if (fwrite(head.data(), 1, head.size(), f) != head.size() || (body_bytes && fwrite(h_body.data(), 1, body_bytes, f) != body_bytes) ||
+        fwrite(tail.data(), 1, tail.size(), f) != tail.size())
+        return fail(BRISK_E_PARAM, "KFF writer: short write");
+    return BRISK_OK;
+}
+
+extern "C" int brisk_write_kff(brisk_t *h, const char *path, uint64_t *n_blocks_out, uint64_t *n_sections_out) {
+    if (!h || !path) return fail(BRISK_E_PARAM, "null argument");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
+    CK(cudaStreamSynchronize(h->stream));
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(BRISK_E_PARAM, std::string("cannot open ") + path);
+    uint64_t nb = 0, ns = 0;
+    int rc = h->P.key_words == 1 ? write_kff_t<1>(h, f, nb, ns) : write_kff_t<2>(h, f, nb, ns);
+    if (fclose(f) != 0 && rc == BRISK_OK) rc = fail(BRISK_E_PARAM, "KFF writer: close failed");
+    if (n_blocks_out) *n_blocks_out = nb;
+    if (n_sections_out) *n_sections_out = ns;
     return rc;
 }
 
@@ -1471,7 +1717,19 @@ extern "C" int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers
     if (nb_buckets) *nb_buckets = v[0];
     if (nb_skmers) *nb_skmers = v[1];
     if (nb_kmers) *nb_kmers = v[2];
-    if (largest_bucket) *largest_bucket = 0;
+    if (largest_bucket) {
+        uint64_t lb = 0;
+        int rc = largest_bucket_kmers(h, lb);
+        if (rc) return rc;
+        if (h->comm && h->comm->n > 1) {  // buckets are disjoint over the ranks: the maximum of the shards' maxima
+            u64 *tmp = part_matrix(h);
+            CK(cudaMemcpyAsync(tmp, &lb, sizeof(lb), cudaMemcpyHostToDevice, h->stream));
+            NCK(g_nccl.AllReduce(tmp, tmp, 1, ncclUint64, ncclMax, h->comm->comm, h->stream));
+            CK(cudaMemcpyAsync(&lb, tmp, sizeof(lb), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+        }
+        *largest_bucket = lb;
+    }
     if (device_bytes) *device_bytes = v[3];
     return BRISK_OK;
 }
@@ -1783,12 +2041,17 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
         delete c;
         return fail(BRISK_E_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
     }
-    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    {   // highest priority: the exchange's small kernels must get SM slots as soon as CTAs of the enumerate launch that is
+        // running on the handle's stream retire, not after the whole launch has been dispatched
+        int lo_p = 0, hi_p = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
+        CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi_p));
+    }
     for (int i = 0; i < COMM_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&c->ev_enum[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
     CK(cudaMallocHost((void **)&c->h_pinned, (16 + 65 * 64) * sizeof(uint64_t)));
-    CK(cudaMalloc((void **)&c->d_gather, (65 + 64 * 65) * sizeof(uint64_t)));
+    CK(cudaMalloc((void **)&c->d_gather, (64 + 65 + 64 + 8 + 64 * 65) * sizeof(uint64_t)));  // partition scratch (totals first) + everybody's rows
     h->comm = c;
     return BRISK_OK;
 }

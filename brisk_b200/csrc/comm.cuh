@@ -86,7 +86,7 @@ struct Comm {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_enum[16] = {}, ev_counts = nullptr, ev_done = nullptr;
     uint64_t *h_pinned = nullptr;  // pinned: [0, 16) record counters after every chunk, [16, 16 + 65 * 64) gathered totals + status
-    u64 *d_gather = nullptr;       // device: [65] this rank's totals + status, then [64][65] everybody's
+    u64 *d_gather = nullptr;       // device: partition scratch whose first n + 1 words are this rank's totals + status, then [64][65] everybody's
     std::vector<uint64_t> h_matrix, send_start, recv_start;
 };
 #define COMM_MAX_CHUNKS 16

@@ -124,9 +124,18 @@ int brisk_dump(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t 
  * On a sharded index every rank dumps its own buckets. */
 int brisk_dump_ordered(brisk_t *h, brisk_kmer *keys, void *data, uint64_t cap, uint64_t *n);
 
+/* BriskWriter::write (brisk/writer.hpp:75-179): the stored set of this handle (its shard of a sharded index) as a KFF
+ * file — header with Brisk's encoding (A 0, C 1, G 3, T 2) and metadata string, the two value sections, then per
+ * bucket id in increasing order and per minimizer one Section_Minimizer whose blocks are superkmers re-assembled from
+ * the stored k-mers (sequence without the minimizer, minimizer position, the DATA of every k-mer), the section index
+ * and the footer.  The reference's blocks are whatever its insertion order compacted; the (k-mer, minimizer position,
+ * DATA) content is the same.  Bucket arithmetic is 64-bit (the reference's `max_mini` overflows at b = 16,
+ * writer.hpp:94).  n_blocks / n_sections (nullable) receive what was written. */
+int brisk_write_kff(brisk_t *h, const char *path, uint64_t *n_blocks, uint64_t *n_sections);
+
 /* Brisk::stats (brisk/Brisk.hpp:194-197, brisk/DenseMenuYo.hpp:545-568). nb_skmers = superkmer records
- * that created at least one k-mer; largest_bucket is not tracked (reported 0): both depend on
- * insertion order in the reference. */
+ * that created at least one k-mer; largest_bucket = the largest number of k-mers stored under one bucket id (the
+ * reference counts the SKL records of a bucket, which depends on its insertion order). */
 int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t *nb_kmers,
                 uint64_t *device_bytes, uint64_t *largest_bucket);
 

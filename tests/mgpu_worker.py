@@ -52,7 +52,9 @@ def main():
             assert np.array_equal(f2, rf2) and np.array_equal(d2, rd2), name
         # insert_reads on a fresh sharded index: newly flags = first occurrence in the global order is not defined
         # across ranks, but their number is: one per distinct k-mer
-        idx2 = Brisk(Parameters(c["k"], c["m"], c["b"]), device=local)
+        # (room for everything up front: the slot ids of the second pass below are compared with the first pass's, and
+        # slot ids are only stable while the store does not grow)
+        idx2 = Brisk(Parameters(c["k"], c["m"], c["b"]), device=local, capacity_hint=4 * c["nb_kmers"])
         idx2.comm_init_torch(dist, rank, world)
         slots, newly = idx2.insert_reads(bases, offs)
         t = torch.tensor([int(newly.sum())], device="cuda")

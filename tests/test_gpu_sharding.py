@@ -73,6 +73,31 @@ def test_virtual_shards_reproduce_the_reference_dump(name):
     assert hits == c["occurrences"]
 
 
+@pytest.mark.parametrize("name", ["synth_cfg3", "synth_cfg5"])
+def test_merged_ordered_dumps_of_two_shards_equal_the_unsharded_ordered_dump(name):
+    """The shards' ordered dumps, merged on bucket id (brisk_b200.merge_ordered_dumps), are the unsharded index's ordered
+    dump element for element: the global order DenseMenuYo::next would walk."""
+    from brisk_b200 import merge_ordered_dumps
+    c = G.case(name)
+    reads = G.reads_of(c)
+    whole = make_index(c)
+    whole.count_reads(*G.flat(reads))
+    want = whole.dump(ordered=True)
+    src = make_index(c)
+    recs, starts = src.partition_reads(*G.flat(reads), 2)
+    parts = []
+    for r in range(2):
+        shard = make_index(c)
+        shard.apply_records(np.ascontiguousarray(recs[int(starts[r]):int(starts[r + 1])]), "count")
+        parts.append(shard.dump(ordered=True))
+    got = merge_ordered_dumps(whole.params, parts)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    st = whole.stats()
+    assert st["largest_bucket"] >= 1 and st["largest_bucket"] == int(np.bincount(
+        np.unique(__import__("brisk_b200").bucket_ids(whole.params, *want[:3]), return_inverse=True)[1]).max())
+
+
 @pytest.mark.parametrize("world", [2])
 def test_nccl_sharded_index_matches_golden(world):
     import torch
