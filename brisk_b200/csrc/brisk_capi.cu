@@ -304,7 +304,7 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     CK(cudaEventCreateWithFlags(&h->offsets_ev, cudaEventDisableTiming));
     CK(cudaMalloc((void **)&h->counters, 8 * sizeof(uint64_t)));
     CK(cudaMemsetAsync(h->counters, 0, 8 * sizeof(uint64_t), h->stream));
-    CK(cudaMalloc((void **)&h->d_rec_count, sizeof(uint64_t)));
+    CK(cudaMalloc((void **)&h->d_rec_count, 32 * sizeof(uint64_t)));  // [0]: the batch's record counter; [16 + c]: chunk c of a pipelined exchange
     {
         std::vector<int2> tab = decycle_group_table(m);
         CK(cudaMalloc((void **)&h->dec_tab, tab.size() * sizeof(int2)));
@@ -342,6 +342,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     if (h->comm) {
         if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
         if (h->comm->stream) cudaStreamDestroy(h->comm->stream);
+        if (h->comm->aux) cudaStreamDestroy(h->comm->aux);
         for (int i = 0; i < COMM_MAX_CHUNKS; i++) if (h->comm->ev_enum[i]) cudaEventDestroy(h->comm->ev_enum[i]);
         if (h->comm->ev_counts) cudaEventDestroy(h->comm->ev_counts);
         if (h->comm->ev_done) cudaEventDestroy(h->comm->ev_done);
@@ -468,34 +469,35 @@ static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
 }
 
 template <int KT, int MT, int RW, bool RING, bool LIT>
-static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
+static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st) {
     typedef typename KM<KT, MT>::hash_t hash_t;
     size_t smem = (RING ? ((size_t)h->P.w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 * 8 : 0) + (ENUM_THREADS / 32) * ENUM_WPOOL * sizeof(u64) +
                   4 * h->P.m * sizeof(double) + 64 * (size_t)h->P.dec_groups * sizeof(int2);
     cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<KT, MT, RW, RING, LIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned blocks = (unsigned)((r1 - r0 + ENUM_THREADS - 1) / ENUM_THREADS);
-    enumerate_kernel<KT, MT, RW, RING, LIT><<<blocks, ENUM_THREADS, smem, h->stream>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
+    enumerate_kernel<KT, MT, RW, RING, LIT><<<blocks, ENUM_THREADS, smem, st>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
     return cudaGetLastError();
 }
 // generic (k, m): run-time parameters; the literal decycling mode (a debug / verification switch) only exists here
 template <int RW>
-static cudaError_t launch_enum_generic(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
+static cudaError_t launch_enum_generic(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st) {
     // k > 32: most window positions of a rescan are recomputed anyway, so the ring only costs shared memory
     if (h->P.literal_decycle)
-        return h->use_ring ? launch_enum_t<0, 0, RW, true, true>(h, B, r0, r1, out) : launch_enum_t<0, 0, RW, false, true>(h, B, r0, r1, out);
-    return h->use_ring ? launch_enum_t<0, 0, RW, true, false>(h, B, r0, r1, out) : launch_enum_t<0, 0, RW, false, false>(h, B, r0, r1, out);
+        return h->use_ring ? launch_enum_t<0, 0, RW, true, true>(h, B, r0, r1, out, st) : launch_enum_t<0, 0, RW, false, true>(h, B, r0, r1, out, st);
+    return h->use_ring ? launch_enum_t<0, 0, RW, true, false>(h, B, r0, r1, out, st) : launch_enum_t<0, 0, RW, false, false>(h, B, r0, r1, out, st);
 }
-static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out) {
+static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st = nullptr) {
+    if (!st) st = h->stream;
     const int k = h->P.k, m = h->P.m, RW = h->P.rec_words;
     if (!h->P.literal_decycle && !(h->flags & BRISK_F_GENERIC_ENUM)) {
         // the parameter sets of BASELINE.json's configurations: k and m compiled in
-        if (k == 63 && m == 21 && RW == 4 && !h->use_ring) return launch_enum_t<63, 21, 4, false, false>(h, B, r0, r1, out);
-        if (k == 64 && m == 23 && RW == 4 && !h->use_ring) return launch_enum_t<64, 23, 4, false, false>(h, B, r0, r1, out);
-        if (k == 31 && m == 15 && RW == 2 && h->use_ring) return launch_enum_t<31, 15, 2, true, false>(h, B, r0, r1, out);
-        if (k == 31 && m == 19 && RW == 2 && h->use_ring) return launch_enum_t<31, 19, 2, true, false>(h, B, r0, r1, out);
+        if (k == 63 && m == 21 && RW == 4 && !h->use_ring) return launch_enum_t<63, 21, 4, false, false>(h, B, r0, r1, out, st);
+        if (k == 64 && m == 23 && RW == 4 && !h->use_ring) return launch_enum_t<64, 23, 4, false, false>(h, B, r0, r1, out, st);
+        if (k == 31 && m == 15 && RW == 2 && h->use_ring) return launch_enum_t<31, 15, 2, true, false>(h, B, r0, r1, out, st);
+        if (k == 31 && m == 19 && RW == 2 && h->use_ring) return launch_enum_t<31, 19, 2, true, false>(h, B, r0, r1, out, st);
     }
-    return RW == 2 ? launch_enum_generic<2>(h, B, r0, r1, out) : RW == 4 ? launch_enum_generic<4>(h, B, r0, r1, out) : launch_enum_generic<6>(h, B, r0, r1, out);
+    return RW == 2 ? launch_enum_generic<2>(h, B, r0, r1, out, st) : RW == 4 ? launch_enum_generic<4>(h, B, r0, r1, out, st) : launch_enum_generic<6>(h, B, r0, r1, out, st);
 }
 
 __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *counts) {
@@ -793,50 +795,68 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
     std::vector<uint64_t> cf;
     if (B.chunk_events || B.n_reads < 65536) cf = B.chunk_first;
     else {
-        // whole waves of the enumerate grid per chunk (8 CTAs of 128 reads per SM), shrinking towards the end:
-        // cuts after about 55 % and all but the last wave (every exchange costs a few hundred microseconds of latency
-        // whatever its size: few chunks)
-        static int sms = 0;
-        if (!sms) { cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device); if (sms <= 0) sms = 148; }
-        const uint64_t wave = (uint64_t)sms * 8 * ENUM_THREADS;
-        const uint64_t T = (B.n_reads + wave - 1) / wave;
-        uint64_t cuts[2] = {(uint64_t)(0.55 * (double)T + 0.5), T - 1};
+        // three chunks shrinking towards the end (50 / 35 / 15 % of the reads): every exchange costs a few hundred
+        // microseconds of latency whatever its size, so few chunks; what stays exposed is the exchange of the last one
+        const double frac[2] = {0.5, 0.85};
         cf.push_back(0);
-        for (int i = 0; i < 2; i++) {
-            const uint64_t r = std::min(cuts[i] * wave, B.n_reads);
-            if (r > cf.back() && r < B.n_reads) cf.push_back(r);
-        }
+        for (int i = 0; i < 2; i++) cf.push_back(((uint64_t)(frac[i] * (double)B.n_reads) / ENUM_THREADS) * ENUM_THREADS);
         cf.push_back(B.n_reads);
     }
     const size_t nc = cf.size() - 1;
     if (nc > COMM_MAX_CHUNKS || n >= 64) return 1;  // (word n of the partition scratch carries the status: n < 64)
-    const uint64_t upper = B.total_bytes;
-    const uint64_t cap = std::min(upper + 1, (uint64_t)(3.0 * (double)upper / (h->P.w + 1)) + B.n_reads + 4096);
+    // every chunk enumerates into its own region of d_recs behind its own counter: the chunks of a device-resident batch
+    // are launched alternately on the handle's stream and on an auxiliary stream, so that the CTAs of chunk c + 1 fill the
+    // SMs while the last CTAs of chunk c drain (separate launches in ONE stream would leave the GPU partly idle at every
+    // chunk boundary), and the records of different chunks never interleave
+    std::vector<uint64_t> base(nc + 1, 0), ccap(nc, 0);
+    for (size_t ci = 0; ci < nc; ci++) {
+        const uint64_t bytes = B.chunk_events ? B.chunk_byte[ci + 1] - B.chunk_byte[ci]
+                                              : (uint64_t)((double)B.total_bytes * (double)(cf[ci + 1] - cf[ci]) / (double)std::max<uint64_t>(1, B.n_reads)) + 1;
+        ccap[ci] = std::min(bytes + 1, (uint64_t)(3.0 * (double)bytes / (h->P.w + 1)) + (cf[ci + 1] - cf[ci]) + 4096);
+        base[ci + 1] = base[ci] + ccap[ci];
+    }
+    const uint64_t cap = base[nc];
     CK(h->d_recs.ensure((cap + 1) * RW * sizeof(uint64_t)));
     CK(h->d_send.ensure((cap + 1) * RW * sizeof(uint64_t)));
     uint64_t recv_cap = cap + cap / 4 + 4096;
     CK(h->d_recv.ensure(recv_cap * RW * sizeof(uint64_t)));
     recv_cap = h->d_recv.cap / (RW * sizeof(uint64_t));
-    CK(cudaMemsetAsync(h->d_rec_count, 0, sizeof(uint64_t), h->stream));
-    EnumOut out;
-    out.recs = (u64 *)h->d_recs.p;
-    out.rec_cap = cap;
-    out.rec_count = (u64 *)h->d_rec_count;
-    out.rec_occ = nullptr;
-    out.kmer_base = nullptr;
+    u64 *counters = (u64 *)h->d_rec_count + 16;
+    CK(cudaMemsetAsync(counters, 0, 16 * sizeof(uint64_t), h->stream));
+    const bool two_streams = !B.chunk_events && nc > 1;
+    if (two_streams) {  // the whole batch is packed first (its bases are resident), then the chunks only enumerate
+        if (B.n_reads) {
+            pack_reads_kernel<<<(unsigned)((B.n_reads + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, 0, B.n_reads, B.d_packed);
+            CK(cudaGetLastError());
+            h->last_launches++;
+        }
+        CK(cudaEventRecord(h->ev[1], h->stream));
+        CK(cudaStreamWaitEvent(c.aux, h->ev[1], 0));
+    }
     for (size_t ci = 0; ci < nc; ci++) {
         const uint64_t r0 = cf[ci], r1 = cf[ci + 1];
+        cudaStream_t st = (two_streams && (ci & 1)) ? c.aux : h->stream;
+        EnumOut out;
+        out.recs = (u64 *)h->d_recs.p + base[ci] * RW;
+        out.rec_cap = ccap[ci];
+        out.rec_count = counters + ci;
+        out.rec_occ = nullptr;
+        out.kmer_base = nullptr;
         if (B.chunk_events) CK(cudaStreamWaitEvent(h->stream, h->chunk_ev[ci], 0));
         if (r1 > r0) {
-            pack_reads_kernel<<<(unsigned)((r1 - r0 + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
-            CK(cudaGetLastError());
-            if (ci == 0) CK(cudaEventRecord(h->ev[1], h->stream));
-            CK(launch_enum(h, B, r0, r1, out));
-            h->last_launches += 2;
-        } else if (ci == 0) CK(cudaEventRecord(h->ev[1], h->stream));
-        CK(cudaMemcpyAsync(c.h_pinned + ci, h->d_rec_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
-        CK(cudaEventRecord(c.ev_enum[ci], h->stream));
+            if (!two_streams) {
+                pack_reads_kernel<<<(unsigned)((r1 - r0 + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
+                CK(cudaGetLastError());
+                h->last_launches++;
+            }
+            if (ci == 0 && !two_streams) CK(cudaEventRecord(h->ev[1], h->stream));
+            CK(launch_enum(h, B, r0, r1, out, st));
+            h->last_launches++;
+        } else if (ci == 0 && !two_streams) CK(cudaEventRecord(h->ev[1], h->stream));
+        CK(cudaMemcpyAsync(c.h_pinned + ci, counters + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(c.ev_enum[ci], st));
     }
+    if (two_streams) for (size_t ci = 1; ci < nc; ci += 2) CK(cudaStreamWaitEvent(h->stream, c.ev_enum[ci], 0));
     CK(cudaEventRecord(h->ev[2], h->stream));
     uint64_t done = 0, recv_total = 0;
     u64 *g_mine = c.d_gather, *g_all = c.d_gather + (64 + 65 + 64 + 8);
@@ -846,9 +866,9 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
         CK(cudaEventSynchronize(c.ev_enum[ci]));
         const uint64_t after = c.h_pinned[ci];
         int status = local_status;
-        if (after > cap) status = 1;  // record buffer overflow: everybody falls back to the unpipelined path
-        const uint64_t r0 = done, r1 = std::min(after, cap), cnt = r1 - r0;
-        done = r1;
+        if (after > ccap[ci]) status = 1;  // record buffer overflow: everybody falls back to the unpipelined path
+        const uint64_t r0 = base[ci], cnt = std::min(after, ccap[ci]);
+        done += cnt;
         CK(cudaStreamWaitEvent(c.stream, c.ev_enum[ci], 0));
         // this rank's row of the gather = the partition's own totals (n words) followed by the status word
         CK(cudaMemsetAsync(g_mine, 0, 65 * sizeof(uint64_t), c.stream));
@@ -967,7 +987,7 @@ static int pregrow(brisk_handle *h, uint64_t incoming, bool worst_case = false) 
     uint64_t est_new = incoming;
     if (h->hint) {
         const uint64_t by_hint = std::min<uint64_t>(incoming, h->hint > h->n_keys ? h->hint - h->n_keys : 0);
-        const uint64_t by_rate = std::min<uint64_t>(incoming, (uint64_t)((1.5 * h->new_rate + 0.02) * (double)incoming));
+        const uint64_t by_rate = std::min<uint64_t>(incoming, (uint64_t)((1.25 * h->new_rate + 0.01) * (double)incoming));
         est_new = std::max(by_hint, by_rate);
     }
     if (worst_case && (h->n_keys + incoming) * 10 > h->cap * 9) {
@@ -1132,10 +1152,14 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         if (rc) return rc;
         CK(cudaEventRecord(h->ev[3], h->stream));
         if (mode != MODE_GET) {
-            // occurrences about to be inserted: this rank's own bytes, or (sharded) the received records times the
-            // k-mers per record of the batch this rank enumerated itself
-            const uint64_t per_rec = n_recs ? (B.total_bytes + n_recs - 1) / n_recs : (uint64_t)h->P.w;
-            rc = pregrow(h, sharded ? X.n * std::min<uint64_t>(per_rec, (uint64_t)h->P.w) : B.total_bytes, with_occ);
+            // occurrences about to be inserted: this rank's own (bytes minus the k - 1 bases every read loses), or (sharded)
+            // the received records times the k-mers per record of the batch this rank enumerated itself
+            const uint64_t lost = B.n_reads * (uint64_t)(h->P.k - 1);
+            const uint64_t own_occ = B.total_bytes > lost ? B.total_bytes - lost : B.total_bytes;
+            const uint64_t per_rec = n_recs ? (own_occ + n_recs - 1) / n_recs : (uint64_t)h->P.w;
+            // (calls that hand slot ids back need an upper bound, not an estimate)
+            if (with_occ) rc = pregrow(h, sharded ? X.n * (uint64_t)h->P.w : B.total_bytes, true);
+            else rc = pregrow(h, sharded ? X.n * std::min<uint64_t>(per_rec, (uint64_t)h->P.w) : own_occ, false);
             if (rc) return rc;
         }
         rc = stage_outputs();
@@ -2047,6 +2071,7 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
         CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
         CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi_p));
     }
+    CK(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
     for (int i = 0; i < COMM_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&c->ev_enum[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
