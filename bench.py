@@ -142,7 +142,19 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------------ CPU reference legs
 def host_reads(W, first, count):
+    """(count, L) uint8 reads of the workload for the CPU legs: generated on the device when there is one (bit-identical
+    to the numpy generator, tests/test_gpu_mid.py, and much faster for the 3 Gbp genome), else with numpy"""
     from brisk_b200 import synth
+    try:
+        import torch
+        if torch.cuda.is_available():
+            if not hasattr(W, "_dgen"):
+                W._dgen = synth.device_genome(W.G, W.seed)
+            out = synth.device_reads(W._dgen, W.L, W.seed, first, count)
+            torch.cuda.synchronize()
+            return out.cpu().numpy().reshape(count, W.L)
+    except Exception:
+        pass
     if not hasattr(W, "_gen"):
         W._gen = synth.genome(W.G, W.seed)
     return synth.reads(W._gen, W.L, W.seed, first, count)

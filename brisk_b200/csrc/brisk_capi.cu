@@ -342,7 +342,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     if (h->comm) {
         if (h->comm->comm) g_nccl.CommDestroy(h->comm->comm);
         if (h->comm->stream) cudaStreamDestroy(h->comm->stream);
-        if (h->comm->aux) cudaStreamDestroy(h->comm->aux);
+        for (int i = 0; i < 2; i++) if (h->comm->aux[i]) cudaStreamDestroy(h->comm->aux[i]);
         for (int i = 0; i < COMM_MAX_CHUNKS; i++) if (h->comm->ev_enum[i]) cudaEventDestroy(h->comm->ev_enum[i]);
         if (h->comm->ev_counts) cudaEventDestroy(h->comm->ev_counts);
         if (h->comm->ev_done) cudaEventDestroy(h->comm->ev_done);
@@ -823,7 +823,11 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
     recv_cap = h->d_recv.cap / (RW * sizeof(uint64_t));
     u64 *counters = (u64 *)h->d_rec_count + 16;
     CK(cudaMemsetAsync(counters, 0, 16 * sizeof(uint64_t), h->stream));
-    const bool two_streams = !B.chunk_events && nc > 1;
+    // development switch BRISK_EXCHANGE_MODE: 1 = chunks one after the other on the handle's stream, 2 = alternating between
+    // the handle's stream and one auxiliary stream, 3 (default) = priority-ordered auxiliary streams
+    static int xmode = -1;
+    if (xmode < 0) { const char *e = getenv("BRISK_EXCHANGE_MODE"); xmode = e ? atoi(e) : 3; }
+    const bool two_streams = !B.chunk_events && nc > 1 && nc <= 3 && xmode >= 2 && (xmode == 2 || c.aux_ordered);
     if (two_streams) {  // the whole batch is packed first (its bases are resident), then the chunks only enumerate
         if (B.n_reads) {
             pack_reads_kernel<<<(unsigned)((B.n_reads + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, 0, B.n_reads, B.d_packed);
@@ -831,11 +835,11 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
             h->last_launches++;
         }
         CK(cudaEventRecord(h->ev[1], h->stream));
-        CK(cudaStreamWaitEvent(c.aux, h->ev[1], 0));
+        for (int i = 0; i < 2; i++) CK(cudaStreamWaitEvent(c.aux[i], h->ev[1], 0));
     }
     for (size_t ci = 0; ci < nc; ci++) {
         const uint64_t r0 = cf[ci], r1 = cf[ci + 1];
-        cudaStream_t st = (two_streams && (ci & 1)) ? c.aux : h->stream;
+        cudaStream_t st = !two_streams ? h->stream : xmode == 2 ? ((ci & 1) ? c.aux[1] : h->stream) : (ci + 1 < nc ? c.aux[ci & 1] : h->stream);
         EnumOut out;
         out.recs = (u64 *)h->d_recs.p + base[ci] * RW;
         out.rec_cap = ccap[ci];
@@ -856,7 +860,7 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
         CK(cudaMemcpyAsync(c.h_pinned + ci, counters + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(c.ev_enum[ci], st));
     }
-    if (two_streams) for (size_t ci = 1; ci < nc; ci += 2) CK(cudaStreamWaitEvent(h->stream, c.ev_enum[ci], 0));
+    if (two_streams) for (size_t ci = 0; ci < nc; ci++) CK(cudaStreamWaitEvent(h->stream, c.ev_enum[ci], 0));
     CK(cudaEventRecord(h->ev[2], h->stream));
     uint64_t done = 0, recv_total = 0;
     u64 *g_mine = c.d_gather, *g_all = c.d_gather + (64 + 65 + 64 + 8);
@@ -2070,8 +2074,11 @@ extern "C" int brisk_comm_init(brisk_t *h, const uint8_t id[128], int rank, int 
         int lo_p = 0, hi_p = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
         CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi_p));
+        // the enumerate chunks before the last one run on streams of decreasing priority (the last one on the handle's
+        // stream): pending CTAs are dispatched chunk after chunk, and the next chunk fills the SMs while one drains
+        for (int i = 0; i < 2; i++) CK(cudaStreamCreateWithPriority(&c->aux[i], cudaStreamNonBlocking, std::min(lo_p, hi_p + 1 + i)));
+        c->aux_ordered = (lo_p - hi_p) >= 3;
     }
-    CK(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
     for (int i = 0; i < COMM_MAX_CHUNKS; i++) CK(cudaEventCreateWithFlags(&c->ev_enum[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));

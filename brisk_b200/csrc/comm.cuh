@@ -84,7 +84,8 @@ struct Comm {
     // The exchange runs on its own stream: while the records of chunk c travel, the handle's stream enumerates chunk
     // c + 1 (brisk_capi.cu: exchange_pipelined).  The host only ever waits on this stream's events.
     cudaStream_t stream = nullptr;
-    cudaStream_t aux = nullptr;  // every other enumerate chunk of a device-resident batch runs here (overlapping launch tails)
+    cudaStream_t aux[2] = {nullptr, nullptr};  // the enumerate chunks before the last one (decreasing priority, overlapping launch tails)
+    bool aux_ordered = false;                  // the device has enough priority levels for that
     cudaEvent_t ev_enum[16] = {}, ev_counts = nullptr, ev_done = nullptr;
     uint64_t *h_pinned = nullptr;  // pinned: [0, 16) record counters after every chunk, [16, 16 + 65 * 64) gathered totals + status
     u64 *d_gather = nullptr;       // device: partition scratch whose first n + 1 words are this rank's totals + status, then [64][65] everybody's
