@@ -136,6 +136,12 @@ class Brisk:
         self._check(self._lib.brisk_write_kff(self._h, str(path).encode(), C.byref(nb), C.byref(ns)))
         return nb.value, ns.value
 
+    def long_read_info(self):
+        """(length limit above which a read is enumerated in segments, warm-up k-mers, repeated segmented launches)"""
+        out = np.zeros(3, np.uint64)
+        self._check(self._lib.brisk_long_read_info(self._h, _ptr(out)))
+        return int(out[0]), int(out[1]), int(out[2])
+
     def checksum(self):
         """(sum of a 64-bit mix of every stored (kmer_s, minimizer_idx, DATA byte), sum of the DATA bytes, number of stored
         k-mers) of this handle's shard; order-independent, the shards' sums add up to the unsharded index's."""

@@ -64,6 +64,9 @@ struct brisk_handle {
     uint32_t data_size = 1;
     uint64_t hint = 0;
     bool use_ring = true;
+    uint32_t long_limit = 2048;   // reads longer than this many bases go through the segmented launch (0: never)
+    uint64_t seg_warm = 256;      // k-mers a segment warms up over before its first k-mer
+    uint64_t seg_retries = 0;     // segmented launches repeated because neighbouring segments disagreed
     bool region_sort = true;
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
@@ -91,7 +94,7 @@ struct brisk_handle {
     double new_rate = 1.0;                           // new keys per incoming occurrence of the last insert
     // scratch
     DevBuf d_bases, d_offsets, d_packed, d_recs, d_rec_occ, d_kmer_base, d_cnt, d_out_slots, d_out_flags, d_out_data,
-        d_kmers, d_cub;
+        d_kmers, d_cub, d_long;
     // partition / exchange (sharded index and the partition entry point)
     DevBuf d_fa_text, d_fa_bases, d_fa_offsets, d_fa_a, d_fa_b, d_fa_chunks;  // FASTA ingest
     DevBuf d_send, d_send_occ, d_recv, d_recv_occ, d_occ_off, d_ret_slots, d_ret_flags, d_ret_data;
@@ -296,6 +299,9 @@ extern "C" int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size,
     h->use_ring = k <= 32;
     if (const char *e = getenv("BRISK_ENUM_RING")) h->use_ring = atoi(e) != 0;  // development switch
     if (const char *e = getenv("BRISK_REGION_SORT")) h->region_sort = atoi(e) != 0;  // development switch
+    if (const char *e = getenv("BRISK_LONG_READ")) h->long_limit = (uint32_t)std::max(0, atoi(e));  // tests: segment shorter reads too
+    if (h->long_limit && h->long_limit < (uint32_t)k) h->long_limit = k;
+    if (const char *e = getenv("BRISK_SEG_WARM")) h->seg_warm = (uint64_t)std::max(1, atoi(e));
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
     for (int i = 0; i < 6; i++) CK(cudaEventCreate(&h->ev[i]));
@@ -335,7 +341,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf *bufs[] = {&h->d_bases, &h->d_offsets, &h->d_packed, &h->d_recs, &h->d_rec_occ, &h->d_kmer_base, &h->d_cnt,
-                      &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_send, &h->d_send_occ,
+                      &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_long, &h->d_send, &h->d_send_occ,
                       &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data,
                       &h->d_fa_text, &h->d_fa_bases, &h->d_fa_offsets, &h->d_fa_a, &h->d_fa_b, &h->d_fa_chunks};
     for (DevBuf *b : bufs) b->release();
@@ -468,36 +474,55 @@ static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
     return BRISK_OK;
 }
 
-template <int KT, int MT, int RW, bool RING, bool LIT>
-static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st) {
+static EnumLong no_long() { EnumLong l; l.list = nullptr; l.cap = 0; l.count = nullptr; l.limit = 0; return l; }
+static EnumSegIn no_segs() { EnumSegIn g; g.segs = nullptr; g.n_segs = 0; g.at0 = nullptr; g.at1 = nullptr; return g; }
+
+template <int KT, int MT, int RW, bool RING, bool LIT, bool SEG>
+static cudaError_t launch_enum_t(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st, EnumLong lg,
+                                 EnumSegIn sg) {
     typedef typename KM<KT, MT>::hash_t hash_t;
     size_t smem = (RING ? ((size_t)h->P.w * ENUM_THREADS * sizeof(hash_t) + 7) / 8 * 8 : 0) + (ENUM_THREADS / 32) * ENUM_WPOOL * sizeof(u64) +
                   4 * h->P.m * sizeof(double) + 64 * (size_t)h->P.dec_groups * sizeof(int2);
-    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<KT, MT, RW, RING, LIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(enumerate_kernel<KT, MT, RW, RING, LIT, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    unsigned blocks = (unsigned)((r1 - r0 + ENUM_THREADS - 1) / ENUM_THREADS);
-    enumerate_kernel<KT, MT, RW, RING, LIT><<<blocks, ENUM_THREADS, smem, st>>>(h->P, B.d_packed, B.d_offsets, r0, r1, out);
+    // one thread per read of [r0, r1), or (SEG) per segment of [0, n_segs)
+    const uint64_t first = SEG ? 0 : r0, end = SEG ? sg.n_segs : r1;
+    unsigned blocks = (unsigned)((end - first + ENUM_THREADS - 1) / ENUM_THREADS);
+    enumerate_kernel<KT, MT, RW, RING, LIT, SEG><<<blocks, ENUM_THREADS, smem, st>>>(h->P, B.d_packed, B.d_offsets, first, end, out, lg, sg);
     return cudaGetLastError();
 }
-// generic (k, m): run-time parameters; the literal decycling mode (a debug / verification switch) only exists here
-template <int RW>
-static cudaError_t launch_enum_generic(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st) {
+// generic (k, m): run-time parameters; the literal decycling mode (a debug / verification switch) and the segmented
+// launch for long reads only exist here
+template <int RW, bool SEG>
+static cudaError_t launch_enum_generic(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st, EnumLong lg,
+                                       EnumSegIn sg) {
     // k > 32: most window positions of a rescan are recomputed anyway, so the ring only costs shared memory
     if (h->P.literal_decycle)
-        return h->use_ring ? launch_enum_t<0, 0, RW, true, true>(h, B, r0, r1, out, st) : launch_enum_t<0, 0, RW, false, true>(h, B, r0, r1, out, st);
-    return h->use_ring ? launch_enum_t<0, 0, RW, true, false>(h, B, r0, r1, out, st) : launch_enum_t<0, 0, RW, false, false>(h, B, r0, r1, out, st);
+        return h->use_ring ? launch_enum_t<0, 0, RW, true, true, SEG>(h, B, r0, r1, out, st, lg, sg)
+                           : launch_enum_t<0, 0, RW, false, true, SEG>(h, B, r0, r1, out, st, lg, sg);
+    return h->use_ring ? launch_enum_t<0, 0, RW, true, false, SEG>(h, B, r0, r1, out, st, lg, sg)
+                       : launch_enum_t<0, 0, RW, false, false, SEG>(h, B, r0, r1, out, st, lg, sg);
 }
-static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st = nullptr) {
+static cudaError_t launch_enum(brisk_handle *h, const ReadBatch &B, uint64_t r0, uint64_t r1, EnumOut out, cudaStream_t st = nullptr,
+                               EnumLong lg = no_long()) {
     if (!st) st = h->stream;
     const int k = h->P.k, m = h->P.m, RW = h->P.rec_words;
+    const EnumSegIn sg = no_segs();
     if (!h->P.literal_decycle && !(h->flags & BRISK_F_GENERIC_ENUM)) {
         // the parameter sets of BASELINE.json's configurations: k and m compiled in
-        if (k == 63 && m == 21 && RW == 4 && !h->use_ring) return launch_enum_t<63, 21, 4, false, false>(h, B, r0, r1, out, st);
-        if (k == 64 && m == 23 && RW == 4 && !h->use_ring) return launch_enum_t<64, 23, 4, false, false>(h, B, r0, r1, out, st);
-        if (k == 31 && m == 15 && RW == 2 && h->use_ring) return launch_enum_t<31, 15, 2, true, false>(h, B, r0, r1, out, st);
-        if (k == 31 && m == 19 && RW == 2 && h->use_ring) return launch_enum_t<31, 19, 2, true, false>(h, B, r0, r1, out, st);
+        if (k == 63 && m == 21 && RW == 4 && !h->use_ring) return launch_enum_t<63, 21, 4, false, false, false>(h, B, r0, r1, out, st, lg, sg);
+        if (k == 64 && m == 23 && RW == 4 && !h->use_ring) return launch_enum_t<64, 23, 4, false, false, false>(h, B, r0, r1, out, st, lg, sg);
+        if (k == 31 && m == 15 && RW == 2 && h->use_ring) return launch_enum_t<31, 15, 2, true, false, false>(h, B, r0, r1, out, st, lg, sg);
+        if (k == 31 && m == 19 && RW == 2 && h->use_ring) return launch_enum_t<31, 19, 2, true, false, false>(h, B, r0, r1, out, st, lg, sg);
     }
-    return RW == 2 ? launch_enum_generic<2>(h, B, r0, r1, out, st) : RW == 4 ? launch_enum_generic<4>(h, B, r0, r1, out, st) : launch_enum_generic<6>(h, B, r0, r1, out, st);
+    return RW == 2 ? launch_enum_generic<2, false>(h, B, r0, r1, out, st, lg, sg)
+                   : RW == 4 ? launch_enum_generic<4, false>(h, B, r0, r1, out, st, lg, sg) : launch_enum_generic<6, false>(h, B, r0, r1, out, st, lg, sg);
+}
+static cudaError_t launch_enum_segments(brisk_handle *h, const ReadBatch &B, EnumOut out, EnumSegIn sg) {
+    const int RW = h->P.rec_words;
+    return RW == 2 ? launch_enum_generic<2, true>(h, B, 0, 0, out, h->stream, no_long(), sg)
+                   : RW == 4 ? launch_enum_generic<4, true>(h, B, 0, 0, out, h->stream, no_long(), sg)
+                             : launch_enum_generic<6, true>(h, B, 0, 0, out, h->stream, no_long(), sg);
 }
 
 __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *counts) {
@@ -506,6 +531,78 @@ __global__ void kmer_counts_kernel(const u64 *offsets, u64 n_reads, int k, u64 *
         u64 len = offsets[i + 1] - offsets[i];
         counts[i] = len >= (u64)k ? len - k + 1 : 0;
     }
+}
+
+// The long reads of a batch (listed in h->d_long by the plain launch), cut into segments of ENUM_SEG_KMERS k-mers
+// (enumerate.cuh: EnumSeg).  A segment warms up from a rescan `warm` k-mers before its first k-mer; the neighbours'
+// states at the segment boundaries are compared, and when any pair differs the long reads are enumerated again with an
+// 8 times longer warm-up, finally with one thread per read (no warm-up at all: exact by construction).  The records go
+// behind the batch's record counter; n_recs is updated.
+static int enumerate_long_reads(brisk_handle *h, const ReadBatch &B, EnumOut out, uint64_t n_long, uint64_t &n_recs) {
+    const uint64_t short_recs = n_recs;
+    u64 *list = (u64 *)h->d_long.p;
+    u64 *mism = (u64 *)h->d_rec_count + 9;
+    DevBuf nseg, sstart, segs, at0, at1, scan_tmp;
+    auto cleanup = [&]() { for (DevBuf *b : {&nseg, &sstart, &segs, &at0, &at1, &scan_tmp}) b->release(); };
+    auto body = [&]() -> int {
+        CK(nseg.ensure((n_long + 1) * sizeof(u64)));
+        CK(sstart.ensure((n_long + 1) * sizeof(u64)));
+        const unsigned lb = (unsigned)((n_long + 1 + 255) / 256);
+        enumerate_seg_count_kernel<<<lb, 256, 0, h->stream>>>(B.d_offsets, list, n_long, h->P.k, (u64 *)nseg.p);
+        size_t tmp = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, (u64 *)nseg.p, (u64 *)sstart.p, (int)(n_long + 1), h->stream));
+        CK(scan_tmp.ensure(tmp));
+        CK(cub::DeviceScan::ExclusiveSum(scan_tmp.p, tmp, (u64 *)nseg.p, (u64 *)sstart.p, (int)(n_long + 1), h->stream));
+        uint64_t n_segs = 0;
+        CK(cudaMemcpyAsync(&n_segs, (u64 *)sstart.p + n_long, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        h->last_launches += 3;
+        if (n_segs == 0) return BRISK_OK;
+        CK(segs.ensure(n_segs * sizeof(EnumSeg)));
+        CK(at0.ensure(n_segs * sizeof(EnumSegState)));
+        CK(at1.ensure(n_segs * sizeof(EnumSegState)));
+        uint64_t warm = h->seg_warm;
+        for (int attempt = 0;; attempt++) {
+            const bool serial = attempt == 3;  // last resort: every long read is one segment
+            EnumSegIn sg;
+            sg.segs = (const EnumSeg *)segs.p; sg.at0 = (EnumSegState *)at0.p; sg.at1 = (EnumSegState *)at1.p;
+            if (!serial) {
+                enumerate_seg_fill_kernel<<<(unsigned)((n_long + 255) / 256), 256, 0, h->stream>>>(B.d_offsets, list, n_long, h->P.k, warm, (const u64 *)sstart.p,
+                                                                                                  (EnumSeg *)segs.p);
+                sg.n_segs = n_segs;
+            } else {
+                // segment size "infinite": reuse the fill kernel's layout with one entry per read
+                std::vector<uint64_t> hl(n_long), ho(B.n_reads + 1);
+                CK(cudaMemcpy(hl.data(), list, n_long * sizeof(u64), cudaMemcpyDeviceToHost));
+                CK(cudaMemcpy(ho.data(), B.d_offsets, (B.n_reads + 1) * sizeof(u64), cudaMemcpyDeviceToHost));
+                std::vector<EnumSeg> hs;
+                for (uint64_t r : hl) {
+                    const uint64_t len = ho[r + 1] - ho[r];
+                    if (len < (uint64_t)h->P.k) continue;
+                    EnumSeg g; g.read = r; g.kmer0 = 0; g.kmer1 = len - h->P.k + 1; g.start = 0;
+                    hs.push_back(g);
+                }
+                CK(cudaMemcpy(segs.p, hs.data(), hs.size() * sizeof(EnumSeg), cudaMemcpyHostToDevice));
+                sg.n_segs = hs.size();
+            }
+            CK(cudaMemsetAsync(mism, 0, sizeof(u64), h->stream));
+            CK(cudaMemcpyAsync(h->d_rec_count, &short_recs, sizeof(u64), cudaMemcpyHostToDevice, h->stream));
+            CK(launch_enum_segments(h, B, out, sg));
+            if (!serial) enumerate_seg_verify_kernel<<<(unsigned)((sg.n_segs + 255) / 256), 256, 0, h->stream>>>(sg.segs, sg.at0, sg.at1, sg.n_segs, mism);
+            CK(cudaGetLastError());
+            h->last_launches += 3;
+            uint64_t bad = 0;
+            CK(cudaMemcpyAsync(&n_recs, h->d_rec_count, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaMemcpyAsync(&bad, mism, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+            h->seg_retries += bad ? 1 : 0;
+            if (!bad || serial) return BRISK_OK;
+            warm *= 8;
+        }
+    };
+    int rc = body();
+    cleanup();
+    return rc;
 }
 
 // enumerates a staged batch into h->d_recs; with_occ also fills d_rec_occ / d_kmer_base
@@ -546,6 +643,13 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
         out.rec_count = (u64 *)h->d_rec_count;
         out.rec_occ = with_occ ? (u64 *)h->d_rec_occ.p : nullptr;
         out.kmer_base = with_occ ? (const u64 *)h->d_kmer_base.p : nullptr;
+        // reads longer than long_limit bases are left out by the plain launch and listed (enumerate.cuh: EnumLong)
+        EnumLong lg = no_long();
+        if (h->long_limit) {
+            CK(h->d_long.ensure((B.n_reads + 1) * sizeof(uint64_t)));
+            lg.list = (u64 *)h->d_long.p; lg.cap = B.n_reads; lg.count = (u64 *)h->d_rec_count + 8; lg.limit = h->long_limit;
+            CK(cudaMemsetAsync(lg.count, 0, sizeof(uint64_t), h->stream));
+        }
         // chunk by chunk: pack + enumerate of a chunk run while the next chunk's bases are still on their way; the
         // records of all chunks accumulate behind the same device counter
         for (size_t c = c0; c < c1; c++) {
@@ -554,12 +658,18 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
             if (c == 0) CK(cudaEventRecord(h->ev[1], h->stream));
             const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
             if (r1 == r0) continue;
-            cudaError_t e = launch_enum(h, B, r0, r1, out);
+            cudaError_t e = launch_enum(h, B, r0, r1, out, nullptr, lg);
             CK(e);
             h->last_launches++;
         }
+        uint64_t n_long = 0;
         CK(cudaMemcpyAsync(&n_recs, h->d_rec_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        if (lg.list) CK(cudaMemcpyAsync(&n_long, lg.count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
+        if (n_long) {
+            int lrc = enumerate_long_reads(h, B, out, n_long, n_recs);
+            if (lrc) return lrc;
+        }
         if (n_recs <= cap) break;
         cap = n_recs;
         if (attempt == 1) return fail(BRISK_E_CUDA, "superkmer count changed between two enumerations");
@@ -1798,6 +1908,14 @@ extern "C" int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uin
     synth_reads_kernel<<<(unsigned)((count * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const unsigned char *)genome, G, L, seed, first, count,
                                                                                                 (unsigned char *)out);
     CK(cudaGetLastError());
+    return BRISK_OK;
+}
+
+// long-read path (enumerate.cuh: EnumSeg): out[0] = reads longer than this many bases are enumerated in segments,
+// out[1] = k-mers of warm-up, out[2] = segmented launches that had to be repeated with a longer warm-up so far
+extern "C" int brisk_long_read_info(brisk_t *h, uint64_t out[3]) {
+    if (!h || !out) return fail(BRISK_E_PARAM, "null argument");
+    out[0] = h->long_limit; out[1] = h->seg_warm; out[2] = h->seg_retries;
     return BRISK_OK;
 }
 

@@ -194,24 +194,74 @@ struct EnumOut {
     const u64 *kmer_base;  // optional [n_reads]: occurrence index of k-mer 0 of each read
 };
 
-// A long read is cut into segments of k-mers that are enumerated by different threads.  Segment s of a
-// read covers the k-mers [kmer0, kmer1); the thread starts rolling `warm` k-mers earlier with a full rescan
-// (get_minimizer on the k-mer, which is the state the reference has right after an "outdated" event) unless kmer0 = 0
-// (the reference's own seed on the (k-1)-mer), or from the exact state in `st` when one is given (pass 2).
+// Long reads.  One thread per read is the right grain for sequencing reads (hundreds of bases), not for a contig or a
+// chromosome handed over by the FASTA entry points: a thread of the plain launch skips any read longer than
+// EnumLong::limit bases and appends its index to a list instead.  Those reads are then cut into segments of
+// ENUM_SEG_KMERS k-mers that are enumerated by different threads (SEG = true).  The state machine of
+// SuperKmerEnumerator::next depends on history (Q4), so a segment that does not start at the read's first base starts
+// `warm` k-mers early from a full rescan (get_minimizer on that k-mer, the state the reference is in right after an
+// "outdated" event) and only emits the superkmers that START inside [kmer0, kmer1), running on until the superkmer that
+// is open at kmer1 has closed.  Every segment writes down its state after the k-mer kmer0 - 1 (its own warm-up) and
+// after kmer1 - 1; the output is exact if, for every pair of neighbours, the state segment s + 1 reached by warming up
+// equals the state segment s arrived at from the read's start (equal states have equal futures; by induction from
+// segment 0, which is exact).  enumerate_seg_verify_kernel counts the pairs that differ; the host then repeats the long
+// reads with a longer warm-up and finally with one thread per read.
+#define ENUM_SEG_KMERS 1024
+struct EnumLong {
+    u64 *list;    // [cap] indices of the reads the plain launch skipped (null: nothing is skipped)
+    u64 cap;
+    u64 *count;   // device counter
+    u32 limit;    // reads longer than this many bases are skipped
+};
 struct EnumSeg {
     u64 read;       // index of the read in the batch
     u64 kmer0;      // first k-mer whose superkmer starts belong to this segment
     u64 kmer1;      // one past the last
-    u64 start;      // k-mer at which the state machine starts (<= kmer0)
+    u64 start;      // k-mer at which the thread starts rolling (kmer0 - warm, or 0)
 };
-struct EnumSegState {  // state of the machine right after k-mer `kmer1 - 1` (pass 1 output) / right before `kmer0` (pass 2 input)
-    u64 H;
-    int pos;
-    int rev;
-    u64 i0;    // first k-mer of the open superkmer
-    int pos0;
-    int pad;
+struct EnumSegState { u64 H; int pos; int rev; };
+struct EnumSegIn {
+    const EnumSeg *segs;   // null: one thread per read
+    u64 n_segs;
+    EnumSegState *at0, *at1;  // [n_segs] state after k-mer kmer0 - 1 / kmer1 - 1
 };
+
+// segments of the long reads: read j of the list gets n_seg[j] = ceil(n_kmers / ENUM_SEG_KMERS) segments
+__global__ void __launch_bounds__(256) enumerate_seg_count_kernel(const u64 *__restrict__ offsets, const u64 *__restrict__ list, u64 n_long,
+                                                                  int k, u64 *__restrict__ n_seg) {
+    const u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j > n_long) return;
+    u64 v = 0;
+    if (j < n_long) {
+        const u64 r = list[j], len = offsets[r + 1] - offsets[r];
+        v = len >= (u64)k ? (len - k + 1 + ENUM_SEG_KMERS - 1) / ENUM_SEG_KMERS : 0;
+    }
+    n_seg[j] = v;
+}
+__global__ void __launch_bounds__(256) enumerate_seg_fill_kernel(const u64 *__restrict__ offsets, const u64 *__restrict__ list, u64 n_long,
+                                                                 int k, u64 warm, const u64 *__restrict__ seg_start, EnumSeg *__restrict__ segs) {
+    const u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_long) return;
+    const u64 r = list[j], len = offsets[r + 1] - offsets[r];
+    if (len < (u64)k) return;
+    const u64 nk = len - k + 1;
+    u64 o = seg_start[j];
+    for (u64 a = 0; a < nk; a += ENUM_SEG_KMERS, o++) {
+        EnumSeg g;
+        g.read = r; g.kmer0 = a; g.kmer1 = a + ENUM_SEG_KMERS < nk ? a + ENUM_SEG_KMERS : nk;
+        g.start = a > warm ? a - warm : 0;
+        segs[o] = g;
+    }
+}
+// neighbours of one read must agree on the state at their common boundary
+__global__ void __launch_bounds__(256) enumerate_seg_verify_kernel(const EnumSeg *__restrict__ segs, const EnumSegState *__restrict__ at0,
+                                                                   const EnumSegState *__restrict__ at1, u64 n_segs, u64 *mismatches) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 >= n_segs) return;
+    if (segs[i].read != segs[i + 1].read) return;
+    const EnumSegState a = at1[i], b = at0[i + 1];
+    if (a.H != b.H || a.pos != b.pos || a.rev != b.rev) atomicAdd((unsigned long long *)mismatches, 1ull);
+}
 
 // ring of order hashes: slot-major, the column is XOR-swizzled with the slot so that a thread writing its own
 // column and a warp reading one thread's column across slots are both free of bank conflicts
@@ -226,10 +276,11 @@ __device__ __forceinline__ int ring_at(int slot, int tid) { return slot * ENUM_T
 // The warps of a CTA only share the read-only tables: every warp stages the descriptors of its own superkmers (slots
 // handed out with a ballot, no atomics) and expands them into records on its own, so there is no CTA barrier after
 // the tables are loaded.
-template <int KT, int MT, int RW, bool RING, bool LIT>
+// SEG  = true : one thread per SEGMENT of a long read (EnumSegIn) instead of one per read.
+template <int KT, int MT, int RW, bool RING, bool LIT, bool SEG>
 __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskParams P, const u64 *__restrict__ packed,
                                                                  const u64 *__restrict__ offsets, u64 read0, u64 n_reads,
-                                                                 EnumOut out) {
+                                                                 EnumOut out, EnumLong lg, EnumSegIn sg) {
     typedef KM<KT, MT> C;
     typedef typename C::mer_t mer_t;
     typedef typename C::hash_t hash_t;
@@ -247,14 +298,39 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
     const int lane = tid & 31;
     const u32 lane_lt = (1u << lane) - 1u;
     u64 *wpool = pool + (tid >> 5) * ENUM_WPOOL;
-    const u64 rid = read0 + (u64)blockIdx.x * ENUM_THREADS + tid;  // this launch covers reads [read0, n_reads) of the batch
-    u32 L = 0;
+    const u64 gid = read0 + (u64)blockIdx.x * ENUM_THREADS + tid;  // this launch covers reads [read0, n_reads) of the batch
+    u64 rid = gid;          // index of the read in the batch
+    u32 L = 0;              // bases this thread consumes
     u64 wstart = 0;
-    if (rid < n_reads) {
-        u64 beg = offsets[rid], end = offsets[rid + 1];
-        u64 len = end - beg;
+    u64 boff = 0;           // SEG: base of the read at which this thread starts rolling
+    u32 seg_k0 = 0, seg_k1 = 0xffffffffu;  // SEG: k-mers (relative to boff) whose superkmer starts this thread emits
+    bool mid = false;       // SEG: the thread does not start at the read's first base
+    if (!SEG) {
+        if (rid < n_reads) {
+            u64 beg = offsets[rid], end = offsets[rid + 1];
+            u64 len = end - beg;
+            wstart = packed_start(beg, rid);
+            if (len >= (u64)k) {  // apps/counter.cpp:233
+                if (lg.list && len > (u64)lg.limit) {  // a long read: left to the segmented launch
+                    const u64 o = atomicAdd((unsigned long long *)lg.count, 1ull);
+                    if (o < lg.cap) lg.list[o] = rid;
+                } else if (len <= 0xffffffffull) {
+                    L = (u32)len;
+                }
+            }
+        }
+    } else if (gid < sg.n_segs) {
+        const EnumSeg g = sg.segs[gid];
+        rid = g.read;
+        const u64 beg = offsets[rid], len = offsets[rid + 1] - beg;
         wstart = packed_start(beg, rid);
-        L = (len >= (u64)k && len <= 0xffffffffull) ? (u32)len : 0u;  // apps/counter.cpp:233
+        boff = g.start;
+        mid = g.start > 0;
+        // run on until the superkmer that is open at kmer1 has closed: at most w - 1 k-mers further
+        const u64 last = g.kmer1 + (u64)(k - m + 1) + (u64)k - 1;
+        L = (u32)((last < len ? last : len) - boff);
+        seg_k0 = (u32)(g.kmer0 - boff);
+        seg_k1 = (u32)(g.kmer1 - boff);
     }
     const u64 *pk = packed + wstart;
     for (int i = tid; i < 4 * m; i += ENUM_THREADS) coef[i] = P.coef[i];
@@ -272,7 +348,7 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
     int q = 0;                // t mod m (the same for every thread)
     const int DEAD_POS = -(1 << 30);
     hash_t H = 0;             // mini_hash
-    int pos = L ? 0 : DEAD_POS;  // mini_pos
+    int pos = L ? (SEG && mid ? k - m : 0) : DEAD_POS;  // mini_pos (a segment that starts inside its read: rescan at its first k-mer)
     int rev = 0;              // reversed
     u32 i0 = 0;               // first k-mer of the open superkmer
     int pos0 = 0;             // mini_pos of that k-mer
@@ -280,24 +356,25 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
     const int rshift = 2 * m - 2;
     const hash_t polyA = C::make_hash((u32)(P.polyA_hash >> 62), (mer_t)(P.polyA_hash & (u64)m_mask));
 
-    auto emit_record = [&](const u64 *rpk, u64 g, u64 d, u64 read_id) {
+    auto emit_record = [&](const u64 *rpk, u64 roff, u64 g, u64 d, u64 read_id) {
         if (out.recs && g < out.rec_cap) {
             const int rvd = (int)(d >> 48) & 1;
             u64 rec[RW];
-            build_record<KT, MT, RW>(P, rpk, (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd != 0, rec);
+            build_record<KT, MT, RW>(P, rpk, roff + (u32)d, (int)(d >> 32) & 255, (int)(d >> 40) & 255, rvd != 0, rec);
             store_record<RW>(out.recs, g, rec);
-            if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[read_id] + (u32)d) << 1) | (u64)rvd;
+            if (out.rec_occ) out.rec_occ[g] = ((out.kmer_base[read_id] + roff + (u32)d) << 1) | (u64)rvd;
         }
     };
     // stages the descriptor of every lane that wants one
     auto append = [&](bool want, u32 a, int n, int p0, int rv) {
+        if (SEG) want = want && a >= seg_k0 && a < seg_k1;  // only the superkmers that start inside the segment
         const unsigned mk = __ballot_sync(FULL, want);
         if (mk) {
             if (want) {
                 const u64 desc = make_desc(a, n, p0, rv, lane);
                 const int slot = pcount + __popc(mk & lane_lt);
                 if (slot < ENUM_WPOOL) wpool[slot] = desc;
-                else emit_record(pk, atomicAdd(out.rec_count, 1ull), desc, rid);  // staging full: emit directly
+                else emit_record(pk, boff, atomicAdd(out.rec_count, 1ull), desc, rid);  // staging full: emit directly
             }
             pcount += __popc(mk);
         }
@@ -315,7 +392,8 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
             const int owner = (int)(d >> 49) & 31;
             const u64 o_start = __shfl_sync(FULL, wstart, owner);
             const u64 o_rid = __shfl_sync(FULL, rid, owner);
-            if (e < cnt) emit_record(packed + o_start, base + e, d, o_rid);
+            const u64 o_off = SEG ? __shfl_sync(FULL, boff, owner) : 0ull;
+            if (e < cnt) emit_record(packed + o_start, o_off, base + e, d, o_rid);
         }
         __syncwarp();
         pcount = 0;
@@ -365,7 +443,7 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
         const bool has_hi = nmax >= 32;  // positions >= 32 hold the all-A pseudo m-mer (Q3)
         u64 cur64 = 0;
         if (!RING) cur64 = hist;
-        else if (kk > 32 && ((req >> lane) & 1u)) cur64 = get_bits64(pk, (u64)t - 31);
+        else if (kk > 32 && ((req >> lane) & 1u)) cur64 = get_bits64(pk, boff + t - 31);
         while (req) {
             const int src = __ffs(req) - 1;
             req &= req - 1;
@@ -402,8 +480,8 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
                 int cs = 0;
                 if (lane == src) {
                     int nlo = kk < 32 ? kk : 32;
-                    u64 lo = get_bases(pk, (u64)t + 1 - nlo, nlo);
-                    u64 hi = kk > 32 ? get_bases(pk, (u64)t + 1 - kk, kk - 32) : 0;
+                    u64 lo = get_bases(pk, boff + t + 1 - nlo, nlo);
+                    u64 hi = kk > 32 ? get_bases(pk, boff + t + 1 - kk, kk - 32) : 0;
                     cs = canonized128(lo, hi, kk) ? 1 : 0;
                 }
                 cs = __shfl_sync(FULL, cs, src);
@@ -428,7 +506,7 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
     //   t >= k - 1           : one k-mer per step
     const u32 e_roll = RING ? (u32)(m - 1) : (u32)(k - 2);
     for (u32 t0 = 0; t0 < maxL; t0 += ENUM_SYNC_STEPS) {
-        if (t0 < L) word = __ldg(pk + (t0 >> 5));  // the 32 bases of this block of steps
+        if (t0 < L) word = SEG ? get_bits64(pk, boff + t0) : __ldg(pk + (t0 >> 5));  // the 32 bases of this block of steps
         const u32 t1 = t0 + ENUM_SYNC_STEPS;
         u32 t = t0;
         for (; t < t1 && t < e_roll; t++) {
@@ -458,7 +536,7 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
                 }
             }
             __syncwarp();
-            const unsigned req = __ballot_sync(FULL, L != 0);
+            const unsigned req = __ballot_sync(FULL, L != 0 && !(SEG && mid));
             if (req) rescans(req, k - 1, t);
             next_q();
             t++;
@@ -488,6 +566,10 @@ __global__ void __launch_bounds__(ENUM_THREADS, 8) enumerate_kernel(const BriskP
             }
             append(boundary && !first, i0, (int)(i - i0), pos0, old_rev);
             if (boundary || first) { i0 = i; pos0 = pos; }
+            if (SEG && L) {  // the state after this k-mer, where the neighbours of the segment compare theirs
+                if (i + 1 == seg_k0) { EnumSegState z; z.H = (u64)H; z.pos = pos; z.rev = rev; sg.at0[gid] = z; }
+                if (i + 1 == seg_k1) { EnumSegState z; z.H = (u64)H; z.pos = pos; z.rev = rev; sg.at1[gid] = z; }
+            }
             if (t + 1 >= minL) {  // some read of the warp may end here: its open superkmer is the last one
                 const bool fin = t + 1 == L;
                 append(fin, i0, (int)(i + 1 - i0), pos0, rev);

@@ -151,6 +151,13 @@ int brisk_synth_genome(void *genome, uint64_t G, uint64_t seed, void *stream);
 int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uint64_t seed, uint64_t first, uint64_t count, void *out,
                       void *stream);
 
+/* Long reads (contigs, chromosomes): a read longer than out[0] bases (2048; environment BRISK_LONG_READ at brisk_create)
+ * is enumerated in segments of 1024 k-mers by different threads, each warming up over out[1] k-mers (BRISK_SEG_WARM)
+ * before its segment; the result is verified against the neighbouring segments' states and repeated with a longer
+ * warm-up (finally with one thread per read) when they disagree — out[2] counts those repeats.  The superkmers are
+ * exactly SuperKmerEnumerator::next's either way.  Reads of 2^32 bases or more are not supported. */
+int brisk_long_read_info(brisk_t *h, uint64_t out[3]);
+
 /* grow the store so that n_keys distinct k-mers fit (the GPU analogue of Brisk::reallocate) */
 int brisk_reserve(brisk_t *h, uint64_t n_keys);
 int brisk_capacity(brisk_t *h, uint64_t *slots);

@@ -37,8 +37,8 @@ def test_store_kernel_loads_a_slot_with_one_256_bit_request_and_prefetches(mode)
     assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in the store kernel"
 
 
-@pytest.mark.parametrize("fun", ["_Z16enumerate_kernelILi63ELi21ELi4ELb0ELb0EEv11BriskParamsPKyS2_yy7EnumOut",
-                                 "_Z16enumerate_kernelILi31ELi15ELi2ELb1ELb0EEv11BriskParamsPKyS2_yy7EnumOut"])
+@pytest.mark.parametrize("fun", ["_Z16enumerate_kernelILi63ELi21ELi4ELb0ELb0ELb0EEv11BriskParamsPKyS2_yy7EnumOut8EnumLong9EnumSegIn",
+                                 "_Z16enumerate_kernelILi31ELi15ELi2ELb1ELb0ELb0EEv11BriskParamsPKyS2_yy7EnumOut8EnumLong9EnumSegIn"])
 def test_enumerate_kernel_keeps_its_state_in_registers(fun):
     sass = _sass(fun)
     assert "enumerate_kernel" in sass
