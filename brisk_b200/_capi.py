@@ -42,6 +42,7 @@ PROTOTYPES = {
     "brisk_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "brisk_owner_of_bucket": (C.c_uint32, [C.c_uint64, C.c_uint8, C.c_uint32]),
     "brisk_write_kff": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p]),
+    "brisk_reparameterise": (C.c_int, [C.c_void_p, C.c_uint8, C.c_uint8]),
     "brisk_long_read_info": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_checksum": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_synth_genome": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]),

@@ -136,6 +136,13 @@ class Brisk:
         self._check(self._lib.brisk_write_kff(self._h, str(path).encode(), C.byref(nb), C.byref(ns)))
         return nb.value, ns.value
 
+    def reallocate(self, new_m=None, new_b=None):
+        """Brisk::reallocate (brisk/Brisk.hpp:202-224): rebuild under (k, m + 2, b + 2) unless told otherwise"""
+        new_m = self.params.m + 2 if new_m is None else new_m
+        new_b = self.params.b + 2 if new_b is None else new_b
+        self._check(self._lib.brisk_reparameterise(self._h, new_m, new_b))
+        self.params = Parameters(self.params.k, new_m, new_b)
+
     def long_read_info(self):
         """(length limit above which a read is enumerated in segments, warm-up k-mers, repeated segmented launches)"""
         out = np.zeros(3, np.uint64)

@@ -19,6 +19,7 @@
 #include "store.cuh"
 #include "sort.cuh"
 #include "kff.cuh"
+#include "reparam.cuh"
 #include "comm.cuh"
 
 static thread_local std::string g_err;
@@ -1908,6 +1909,65 @@ extern "C" int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uin
     synth_reads_kernel<<<(unsigned)((count * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const unsigned char *)genome, G, L, seed, first, count,
                                                                                                 (unsigned char *)out);
     CK(cudaGetLastError());
+    return BRISK_OK;
+}
+
+// Brisk::reallocate (brisk/Brisk.hpp:202-224): the handle rebuilt under (k, new_m, new_b) — the reference always goes to
+// (m + 2, b + 2).  See reparam.cuh for the semantics.
+extern "C" int brisk_reparameterise(brisk_t *h, uint8_t new_m, uint8_t new_b) {
+    if (!h) return fail(BRISK_E_PARAM, "null handle");
+    std::lock_guard<std::recursive_mutex> lock(h->mu);
+    CK(cudaSetDevice(h->device));
+    SETTLE_PENDING(h);
+    if (h->comm && h->comm->n > 1) return fail(BRISK_E_PARAM, "re-parameterisation of a sharded index is not supported (the owner of a k-mer changes with its bucket)");
+    if (h->cap >= (1ull << 40)) return fail(BRISK_E_CAPACITY, "table too large");
+    BriskParams P2;
+    if (fill_params(P2, h->P.k, new_m, new_b, h->flags) != BRISK_OK) return fail(BRISK_E_PARAM, "bad parameters: need m odd, m < k, m <= 31, 1 <= b <= min(m, 16)");
+    if (P2.rec_words > BRISK_MAX_RW) return fail(BRISK_E_PARAM, "bad parameters");
+    CK(cudaStreamSynchronize(h->stream));
+    // new grouped decycling tables, bucket bitmap, table of the same capacity, priorities
+    std::vector<int2> tab = decycle_group_table(new_m);
+    int2 *new_dec = nullptr;
+    CK(cudaMalloc((void **)&new_dec, tab.size() * sizeof(int2)));
+    CK(cudaMemcpy(new_dec, tab.data(), tab.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    P2.dec_tab = new_dec;
+    P2.dec_groups = (new_m + 2) / 3;
+    const uint64_t new_words = (((uint64_t)1 << (2 * new_b)) + 31) / 32;
+    uint32_t *new_bits = nullptr, *new_special = nullptr;
+    CK(cudaMalloc((void **)&new_bits, new_words * sizeof(uint32_t)));
+    CK(cudaMemsetAsync(new_bits, 0, new_words * sizeof(uint32_t), h->stream));
+    if (h->flags & BRISK_F_MANAGED) CK(cudaMallocManaged((void **)&new_special, 64 * sizeof(uint32_t)));
+    else CK(cudaMalloc((void **)&new_special, 64 * sizeof(uint32_t)));
+    CK(cudaMemsetAsync(new_special, 0, 64 * sizeof(uint32_t), h->stream));
+    void *ns = nullptr;
+    unsigned char *nd = nullptr;
+    uint32_t *ncnt = nullptr;
+    int rc = alloc_table(h, h->cap, &ns, &nd, &ncnt);
+    if (rc) return rc;
+    DevBuf prio;
+    CK(prio.ensure((h->cap + 64) * sizeof(u64)));
+    CK(cudaMemsetAsync(prio.p, 0, (h->cap + 64) * sizeof(u64), h->stream));
+    CK(cudaMemsetAsync(h->counters, 0, 3 * sizeof(uint64_t), h->stream));
+    StoreView from = view_of(h), to = from;
+    to.slots = ns; to.data = nd; to.cnt = ncnt; to.special = new_special; to.bucket_bits = new_bits;
+    const unsigned blocks = (unsigned)std::min<uint64_t>((h->cap + 255) / 256, 148 * 16);
+    if (h->P.key_words == 1) reparam_insert_kernel<1><<<blocks, 256, 0, h->stream>>>(P2, from, to, 64, (u64 *)prio.p);
+    else reparam_insert_kernel<2><<<blocks, 256, 0, h->stream>>>(P2, from, to, 64, (u64 *)prio.p);
+    reparam_data_kernel<<<blocks, 256, 0, h->stream>>>(from, to, 64, (const u64 *)prio.p);
+    CK(cudaGetLastError());
+    uint64_t c[3];
+    CK(cudaMemcpyAsync(c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    prio.release();
+    if (c[1]) return fail(BRISK_E_FULL, "re-parameterisation could not seat every k-mer");  // (same capacity, fewer or as many keys: not expected)
+    cudaFree(h->slots); cudaFree(h->cnt); if (h->data) cudaFree(h->data);
+    cudaFree(h->special); cudaFree(h->bucket_bits); cudaFree(h->dec_tab);
+    h->slots = ns; h->data = nd; h->cnt = ncnt; h->special = new_special; h->bucket_bits = new_bits; h->bitmap_words = new_words;
+    h->dec_tab = new_dec;
+    h->P = P2;
+    h->n_keys = c[0];
+    h->n_new_recs = 0;
+    h->use_ring = h->P.k <= 32;
     return BRISK_OK;
 }
 

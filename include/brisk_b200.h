@@ -151,6 +151,13 @@ int brisk_synth_genome(void *genome, uint64_t G, uint64_t seed, void *stream);
 int brisk_synth_reads(const void *genome, uint64_t G, uint32_t L, uint64_t seed, uint64_t first, uint64_t count, void *out,
                       void *stream);
 
+/* Brisk::reallocate (brisk/Brisk.hpp:202-224, which always goes to m + 2, b + 2): the handle rebuilt under
+ * (k, new_m, new_b).  Every stored kmer_s keeps its value and DATA; its minimizer_idx is recomputed by update_kmer
+ * (brisk/Kmers.cpp:88-97: the literal get_minimizer with the new m, mirrored when it reports the reverse strand).  Old
+ * entries that only differed in their minimizer_idx become one entry (the reference keeps the DATA of the one it
+ * enumerates last; here: of the one with the largest old minimizer_idx).  Single-GPU handles only. */
+int brisk_reparameterise(brisk_t *h, uint8_t new_m, uint8_t new_b);
+
 /* Long reads (contigs, chromosomes): a read longer than out[0] bases (2048; environment BRISK_LONG_READ at brisk_create)
  * is enumerated in segments of 1024 k-mers by different threads, each warming up over out[1] k-mers (BRISK_SEG_WARM)
  * before its segment; the result is verified against the neighbouring segments' states and repeated with a longer

@@ -15,6 +15,7 @@
 //   ref_dump hash  reads.txt k m b out.bin     bfc_hash_64(canonical m-mer) per m-mer offset
 //   ref_dump count reads.txt k m b out.bin     count like apps/counter.cpp, dump the index
 //   ref_dump query reads.txt k m b out.bin q.txt   count reads.txt, then query q.txt
+//   ref_dump realloc reads.txt k m b out.bin   count, then Brisk::reallocate() to (k, m + 2, b + 2), dump the index
 //   ref_dump time  reads.txt k m b threads [max_reads]   timed count (hot path only)
 //   ref_dump steps reads.txt k m b threads reads_per_step n_steps [dump.bin|- [decoy.txt]]
 //                  step j = count chunk j (count_sequence) then query chunk j-1 (query_sequence), timed;
@@ -148,10 +149,12 @@ int main(int argc, char **argv) {
         return 0;
     }
 
-    if (mode == "count" || mode == "query") {
+    if (mode == "count" || mode == "query" || mode == "realloc") {
         vector<string> reads = load_reads(argv[2]);
         Brisk<uint8_t> index(params);
         for (string &s : reads) count_read(index, s);
+        // realloc: Brisk::reallocate (brisk/Brisk.hpp:202-224) rebuilds the index under (k, m + 2, b + 2) before the dump
+        if (mode == "realloc") { index.reallocate(); m = index.params.m; }
         // read the index back the way verif_counts does (apps/counter.cpp:90-104)
         vector<DumpRec> recs;
         kmer_full km(0, 0, m, params.dede);
