@@ -270,8 +270,14 @@ public:
     void stats(uint64_t &nb_buckets, uint64_t &nb_skmers, uint64_t &nb_kmers, uint64_t &memory_usage, uint64_t &largest_bucket) const {
         brisk_check(brisk_stats(menu, &nb_buckets, &nb_skmers, &nb_kmers, &memory_usage, &largest_bucket));
     }
-    // the GPU analogue of Brisk::reallocate (brisk/Brisk.hpp:88-97): make room for n_keys distinct k-mers
+    // capacity growth of the GPU table: make room for n_keys distinct k-mers
     void reserve(uint64_t n_keys) { brisk_check(brisk_reserve(menu, n_keys)); }
+    // Brisk::reallocate (brisk/Brisk.hpp:202-224): the index rebuilt under (k, m + 2, b + 2)
+    void reallocate() {
+        brisk_check(brisk_reparameterise(menu, (uint8_t)(params.m + 2), (uint8_t)(params.b + 2)));
+        params = Parameters(params.k, (uint8_t)(params.m + 2), (uint8_t)(params.b + 2));
+        have_snap_ = false;
+    }
     // count_reads / insert_reads return once their input is consumed; sync() waits for the store to be at rest and
     // reports a deferred store-full error (every call that reads the store does the same implicitly)
     void sync() { brisk_check(brisk_sync(menu)); }
@@ -324,4 +330,17 @@ private:
     std::vector<brisk_kmer> snap_;
     size_t cursor_ = 0;
     bool have_snap_ = false;
+};
+
+// BriskWriter (brisk/writer.hpp:11-20): the index as a KFF file.  apps/counter.cpp:407-411 compiles unchanged:
+//     BriskWriter writer(outfile); writer.write(counter); writer.close();
+class BriskWriter {
+public:
+    explicit BriskWriter(std::string filename) : filename_(std::move(filename)) {}
+    template <class DATA>
+    void write(Brisk<DATA> &index) { brisk_check(brisk_write_kff(index.menu, filename_.c_str(), nullptr, nullptr)); }
+    void close() {}
+
+private:
+    std::string filename_;
 };

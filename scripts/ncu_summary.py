@@ -48,9 +48,11 @@ def main():
                 i = hdr.index(w)
                 lines.append("| %s | %s | %s |" % (w, r[i], units[i]))
         try:
-            rd = float(r[hdr.index("dram__bytes_read.sum")].replace(",", ""))
-            wr = float(r[hdr.index("dram__bytes_write.sum")].replace(",", ""))
-            lines.append("| **traffic (dram read + write)** | %.6g | %s |" % (rd + wr, units[hdr.index("dram__bytes_read.sum")]))
+            mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+            ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            rd = float(r[ri].replace(",", "")) * mult[units[ri]]
+            wr = float(r[wi].replace(",", "")) * mult[units[wi]]
+            lines.append("| **traffic (dram read + write)** | %.6g | Gbyte |" % ((rd + wr) / 1e9))
         except Exception:
             pass
         st = []

@@ -70,7 +70,7 @@ static void dump(Brisk<uint8_t> &counter, const char *tag) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 5) { fprintf(stderr, "usage: counter_mirror reads.txt k m b\n"); return 2; }
+    if (argc < 5) { fprintf(stderr, "usage: counter_mirror reads.txt k m b [out.kff]\n"); return 2; }
     try {
         Parameters params(atoi(argv[2]), atoi(argv[3]), atoi(argv[4]));
         vector<string> reads;
@@ -123,6 +123,17 @@ int main(int argc, char **argv) {
             }
             printf("WIDE kmers %llu sum %llu occurrences %llu bad %llu\n", (unsigned long long)n, (unsigned long long)sum,
                    (unsigned long long)occurrences, (unsigned long long)bad);
+        }
+        // the KFF dump exactly as apps/counter.cpp:407-411 writes it, then Brisk::reallocate (brisk/Brisk.hpp:202-224)
+        if (argc > 5) {
+            BriskWriter writer(argv[5]);
+            writer.write(batched);
+            writer.close();
+            batched.reallocate();
+            uint64_t nb_buckets, nb_skmers, nb_kmers, memory, largest;
+            batched.stats(nb_buckets, nb_skmers, nb_kmers, memory, largest);
+            printf("REALLOC m %u b %u kmers %llu buckets %llu\n", (unsigned)batched.params.m, (unsigned)batched.params.b, (unsigned long long)nb_kmers,
+                   (unsigned long long)nb_buckets);
         }
         // absent key -> NULL (brisk/DenseMenuYo.hpp:331-333)
         kmer_full absent((kint)0x123456789abcdefull, 3, params.m, params.dede);

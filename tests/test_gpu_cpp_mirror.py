@@ -36,7 +36,8 @@ def test_cpp_mirror_reproduces_reference_dump(binary, name, tmp_path):
     reads = G.reads_of(c)
     path = tmp_path / "reads.txt"
     path.write_bytes(b"\n".join(reads) + b"\n")
-    res = subprocess.run([binary, str(path), str(c["k"]), str(c["m"]), str(c["b"])], capture_output=True, text=True, timeout=600)
+    kff = tmp_path / "out.kff"
+    res = subprocess.run([binary, str(path), str(c["k"]), str(c["m"]), str(c["b"]), str(kff)], capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "EXCEPTION" not in res.stdout and "ERROR" not in res.stdout
     for tag in ("LEGACY", "BATCHED"):
@@ -49,3 +50,10 @@ def test_cpp_mirror_reproduces_reference_dump(binary, name, tmp_path):
     assert ql[0].split()[2:] == ql[1].split()[2:]
     assert "ABSENT null" in res.stdout
     assert "WIDE kmers %d sum %d occurrences %d bad 0" % (c["nb_kmers"], c["occurrences"], c["occurrences"]) in res.stdout
+    # BriskWriter through the mirror: the file holds the golden k-mers (tests/kff_reader.py); reallocate went to (m + 2, b + 2)
+    from kff_reader import kmers_of, read_kff
+    km = kmers_of(read_kff(str(kff)))
+    lo = np.array([x[0] & 0xFFFFFFFFFFFFFFFF for x in km], np.uint64)
+    hi = np.array([x[0] >> 64 for x in km], np.uint64)
+    assert G.dump_sha(lo, hi, np.array([x[1] for x in km], np.uint8), np.array([x[2][0] for x in km], np.uint8)) == c["dump_sha256"]
+    assert "REALLOC m %d b %d kmers " % (c["m"] + 2, c["b"] + 2) in res.stdout
