@@ -65,7 +65,9 @@ typedef struct {
 
 /* Parameters(k,m,b) + Brisk<DATA>(params): brisk/parameters.hpp:24-34, brisk/Brisk.hpp:47-52.
  * data_size = sizeof(DATA) (1 for the counter's uint8_t).  capacity_hint = expected number of
- * distinct stored k-mers (0 = size from the batches seen).  device < 0 = current device. */
+ * distinct stored k-mers (0 = size from the batches seen); the table is laid out for a load factor of about 0.25 at
+ * that many keys when it takes less than a quarter of the device's free memory (0.5 otherwise) and grows on its own
+ * beyond.  device < 0 = current device. */
 int brisk_create(uint8_t k, uint8_t m, uint8_t b, uint32_t data_size, int device, uint64_t capacity_hint,
                  uint32_t flags, brisk_t **out);
 int brisk_destroy(brisk_t *h);
