@@ -34,21 +34,22 @@ __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__
     const u64 len = end - beg;
     u64 *out = packed + packed_start(beg, r);
     const unsigned char *src = bases + beg;
-    // a warp packs 128 bases (4 words) per iteration: lane -> 4 consecutive bases
-    for (u64 base0 = 0; base0 < len; base0 += 128) {
-        u64 p = base0 + 4 * (u64)lane;
+    // a warp packs 256 bases (8 words) per iteration, lane -> 8 consecutive bases: the eight byte loads of a lane are
+    // independent, so a read of up to 256 bases costs ONE memory round trip (the kernel is latency-bound: two
+    // dependent offset loads, then the bases)
+    for (u64 base0 = 0; base0 < len; base0 += 256) {
+        const u64 p = base0 + 8 * (u64)lane;
+        u32 c[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) c[j] = (p + j < len) ? (u32)src[p + j] : 0u;
         u32 v = 0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            u32 c = (p + j < len) ? (u32)src[p + j] : 0u;
-            v = (v << 2) | ((c >> 1) & 3u);
-        }
-        // lane g*8+i holds bases [32g+4i, 32g+4i+4): place at bits (7-i)*8 of word g
-        u64 x = (u64)v << (8 * (7 - (lane & 7)));
+        for (int j = 0; j < 8; j++) v = (v << 2) | ((c[j] >> 1) & 3u);
+        // lane g*4+i holds bases [32g+8i, 32g+8i+8): place its 16 bits at bits (3-i)*16 of word g
+        u64 x = (u64)v << (16 * (3 - (lane & 3)));
         x |= __shfl_xor_sync(0xffffffffu, x, 1);
         x |= __shfl_xor_sync(0xffffffffu, x, 2);
-        x |= __shfl_xor_sync(0xffffffffu, x, 4);
-        if ((lane & 7) == 0 && base0 + 32 * (u64)(lane >> 3) < len) out[(base0 >> 5) + (lane >> 3)] = x;
+        if ((lane & 3) == 0 && base0 + 32 * (u64)(lane >> 2) < len) out[(base0 >> 5) + (lane >> 2)] = x;
     }
 }
 
