@@ -8,12 +8,15 @@
 //     H   inside a header line               Lb / Lr  at a line start, last sequence byte was a cut (b) / a base (r)
 //                                            Sb / Sr  inside a sequence line, same b / r
 // and automaton transitions compose associatively, so the text is processed as a two-level scan:
-//   fasta_summarize_kernel : every thread runs its 128-byte chunk from all 5 entry states (exit state, bases emitted,
-//                            runs started per entry state); the CTA composes its 256 chunks into one tile summary
+//   fasta_summarize_kernel : every thread classifies its 128-byte chunk into three 128-bit masks (newline, '>', base;
+//                            one shared-memory table lookup per byte) and derives, with carry-propagating mask
+//                            arithmetic, the exit state, bases emitted and runs started for all 5 entry states
+//                            (fa_masks); the CTA composes its 256 chunks into one tile summary
 //   fasta_tiles_kernel     : one CTA composes the tile summaries from the start state H -> entry state, first base
 //                            index and first run index of every tile; totals; the closing offset
-//   fasta_emit_kernel      : every CTA reloads its chunk summaries, scans them, and every thread replays its chunk from
-//                            its now known entry state, writing upper-cased bases densely and one offset per run
+//   fasta_emit_kernel      : every CTA reloads its chunk summaries, scans them, and every thread recomputes the masks of its
+//                            chunk for its now known entry state, writing the selected bytes upper-cased and densely,
+//                            and one offset per run
 // The text is read twice, the bases written once, a 16-byte summary per 128-byte chunk written and read back:
 // about 3.3 bytes of HBM traffic per text byte.
 #pragma once
@@ -84,20 +87,6 @@ struct FaCompose {
     }
 };
 
-// 5 bits (one per entry state) -> 5 bytes of 0 / 1
-__device__ __forceinline__ u64 fa_spread(u32 m) {
-    return (((((u64)m * 0x0101010101ull) & 0x1008040201ull) + 0x7f7f7f7f7full) >> 7) & 0x0101010101ull;
-}
-
-// Summary of the chunk [beg, beg + FA_CHUNK) cut at n.  The five entry states are run TOGETHER as three 5-bit masks
-// (bit s = the run that entered in state s): Hm = inside a header line, Lm = at a line start, Rm = the last sequence byte
-// was a base.  Every byte class is then a handful of mask operations:
-//   '\n'  : headers end (their b / r memory restarts at b), everybody is at a line start
-//   '>'   : the runs at a line start enter a header; for the others it is a cut
-//   base  : every run outside a header emits it; it opens a read where Rm is clear
-//   other : a cut
-// Bases are counted in one scalar between changes of Hm (all runs outside a header emit the same bases) and flushed
-// into the five byte-wide counters when Hm changes; read starts are rare and added directly.
 struct FaChunkBytes {  // the chunk's bytes in registers (eight 16-byte loads when the text is 16-byte aligned)
     uint4 q[FA_CHUNK / 16];
 };
@@ -118,51 +107,102 @@ __device__ __forceinline__ void fa_load_chunk(const unsigned char *__restrict__ 
         }
     }
 }
-__device__ __forceinline__ unsigned char fa_byte(const FaChunkBytes &B, int i, int j) {  // byte j of quad i (static i)
-    const u32 w = j < 4 ? B.q[i].x : j < 8 ? B.q[i].y : j < 12 ? B.q[i].z : B.q[i].w;
-    return (unsigned char)(w >> (8 * (j & 3)));
+
+// ---- the automaton over a chunk as mask arithmetic ---------------------------------------------------------------
+// bit i of a 128-bit mask = byte i of the chunk.  Classification: one lookup per byte in a 256-entry table whose
+// entries carry the class bit at bit 0 (newline), 8 ('>') or 16 (base): eight lookups, each shifted by its byte's
+// position, add up to three 8-bit masks at once.
+struct M128 { u64 lo, hi; };
+__device__ __forceinline__ M128 m_and(M128 a, M128 b) { return {a.lo & b.lo, a.hi & b.hi}; }
+__device__ __forceinline__ M128 m_or(M128 a, M128 b) { return {a.lo | b.lo, a.hi | b.hi}; }
+__device__ __forceinline__ M128 m_andn(M128 a, M128 b) { return {a.lo & ~b.lo, a.hi & ~b.hi}; }  // a & ~b
+__device__ __forceinline__ M128 m_shl1(M128 a, u64 in) { return {(a.lo << 1) | in, (a.hi << 1) | (a.lo >> 63)}; }
+__device__ __forceinline__ M128 m_add(M128 a, M128 b) {
+    M128 r;
+    r.lo = a.lo + b.lo;
+    r.hi = a.hi + b.hi + (r.lo < a.lo ? 1ull : 0ull);
+    return r;
+}
+__device__ __forceinline__ u32 m_bit(M128 a, int i) { return (u32)((i < 64 ? a.lo >> i : a.hi >> (i - 64)) & 1ull); }
+__device__ __forceinline__ u32 m_popc(M128 a) { return __popcll(a.lo) + __popcll(a.hi); }
+__device__ __forceinline__ M128 m_first(int n) {  // bits [0, n)
+    M128 r;
+    r.lo = n >= 64 ? ~0ull : ((1ull << n) - 1);
+    r.hi = n <= 64 ? 0ull : (n >= 128 ? ~0ull : ((1ull << (n - 64)) - 1));
+    return r;
 }
 
-__device__ __forceinline__ FaSummary fa_chunk_summary(const FaChunkBytes &B, u64 beg, u64 n) {
-    u32 Hm = 1u, Lm = 6u, Rm = 20u;  // entry states H, Lb, Lr, Sb, Sr = bits 0..4
-    u32 run = 0;                     // bases seen since Hm last changed
-    u64 nbp = 0, nrp = 0;            // 5 byte-wide counters each
-    const int len = beg >= n ? 0 : (n - beg < FA_CHUNK ? (int)(n - beg) : FA_CHUNK);
+__device__ __forceinline__ void fa_init_lut(u32 *lut) {  // [256], filled by the CTA
+    for (int c = threadIdx.x; c < 256; c += blockDim.x)
+        lut[c] = (c == '\n' ? 1u : 0u) | (c == '>' ? 1u << 8 : 0u) | (fasta_is_base((unsigned char)c) ? 1u << 16 : 0u);
+}
+struct FaChunkMasks { M128 N, G, B; };
+__device__ __forceinline__ FaChunkMasks fa_classify(const FaChunkBytes &Bt, const u32 *lut) {
+    FaChunkMasks m;
+    u64 n[2] = {0, 0}, g[2] = {0, 0}, b[2] = {0, 0};
 #pragma unroll
     for (int i = 0; i < FA_CHUNK / 16; i++) {
+        const u32 w[4] = {Bt.q[i].x, Bt.q[i].y, Bt.q[i].z, Bt.q[i].w};
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-            if (16 * i + j < len) {
-                const u32 cls = fasta_class(fa_byte(B, i, j));
-                if (cls == FA_BASE) {
-                    const u32 st = ~Hm & ~Rm & 31u;
-                    if (st) nrp += fa_spread(st);
-                    run++;
-                    Rm = 31u;
-                    Lm = 0u;
-                } else {
-                    const u32 newH = cls == FA_NL ? 0u : cls == FA_GT ? (Hm | Lm) : Hm;
-                    if (newH != Hm) {
-                        nbp += fa_spread(~Hm & 31u) * run;
-                        run = 0;
-                    }
-                    Rm = cls == FA_NL ? (Rm & ~Hm) : 0u;
-                    Lm = cls == FA_NL ? 31u : 0u;
-                    Hm = newH;
-                }
-            }
+        for (int h = 0; h < 2; h++) {  // 8 bytes: bits 0..7 / 8..15 / 16..23 of acc = their newline / '>' / base masks
+            u32 acc = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc += lut[(w[2 * h + (j >> 2)] >> (8 * (j & 3))) & 255u] << j;
+            const int grp = 2 * i + h;  // 8-byte group 0..15
+            n[grp >> 3] |= (u64)(acc & 255u) << (8 * (grp & 7));
+            g[grp >> 3] |= (u64)((acc >> 8) & 255u) << (8 * (grp & 7));
+            b[grp >> 3] |= (u64)((acc >> 16) & 255u) << (8 * (grp & 7));
         }
     }
-    nbp += fa_spread(~Hm & 31u) * run;
+    m.N = {n[0], n[1]}; m.G = {g[0], g[1]}; m.B = {b[0], b[1]};
+    return m;
+}
+// The chunk of n bytes entered in state `entry`: K = the bases that are emitted, St = the ones that open a run, and the
+// exit state.  (Checked against the byte-by-byte automaton above for every entry state on random chunks; the derivation:
+//   header lines  HL : runs of non-newline bytes that start at a '>' on a line start, or at byte 0 when the chunk is
+//                      entered inside a header — adding the start bits to the non-newline mask ripples a carry through
+//                      exactly those runs and clears them;
+//   emitted       K  : bases outside header lines;
+//   run starts    St : emitted bases whose previous byte is neither an emitted base nor a run of transparent newlines
+//                      that follows one (the newline that ends a header line is a cut, not transparent) — the same
+//                      carry trick over the transparent newlines, with the entry state's b / r memory as carry-in.)
+__device__ __forceinline__ u32 fa_masks(const FaChunkMasks &C, int n, u32 entry, M128 &K, M128 &St) {
+    const M128 V = m_first(n);
+    const u64 inH = entry == FA_H, atL = (entry == FA_LB || entry == FA_LR), r = (entry == FA_LR || entry == FA_SR);
+    const M128 N = m_and(C.N, V);
+    const M128 M = m_andn(V, N);
+    const M128 LS = m_and(m_shl1(N, atL), V);
+    M128 Sx = m_and(C.G, LS);
+    Sx.lo |= inH & M.lo & 1ull;
+    const M128 HL = m_andn(M, m_add(M, Sx));
+    M128 hn = m_shl1(HL, 0);
+    hn.lo |= inH;
+    const M128 HN = m_and(N, hn);
+    K = m_andn(m_and(C.B, V), HL);
+    const M128 T = m_andn(N, HN);
+    const u64 reff = r & (inH ^ 1ull);
+    const M128 S2 = m_and(m_shl1(K, reff), T);
+    const M128 F = m_andn(T, m_add(T, S2));
+    const M128 KF = m_or(K, F);
+    St = m_andn(K, m_shl1(KF, reff));
+    if (n == 0) return entry;
+    const int last = n - 1;
+    if (m_bit(HL, last)) return FA_H;
+    const u32 l = m_bit(N, last), rb = m_bit(KF, last);
+    return l ? (rb ? FA_LR : FA_LB) : (rb ? FA_SR : FA_SB);
+}
+
+__device__ __forceinline__ FaSummary fa_chunk_summary(const FaChunkMasks &C, u64 beg, u64 n) {
+    const int len = beg >= n ? 0 : (n - beg < FA_CHUNK ? (int)(n - beg) : FA_CHUNK);
     FaSummary f;
     f.exits = 0;
 #pragma unroll
-    for (int s = 0; s < 5; s++) {
-        const u32 h = (Hm >> s) & 1u, l = (Lm >> s) & 1u, r = (Rm >> s) & 1u;
-        const u32 st = h ? FA_H : (l ? FA_LB + r : FA_SB + r);
-        f.exits |= st << (3 * s);
-        f.nb[s] = (u32)(nbp >> (8 * s)) & 255u;
-        f.nr[s] = (u32)(nrp >> (8 * s)) & 255u;
+    for (u32 s = 0; s < 5; s++) {
+        M128 K, St;
+        const u32 ex = fa_masks(C, len, s, K, St);
+        f.exits |= ex << (3 * s);
+        f.nb[s] = m_popc(K);
+        f.nr[s] = m_popc(St);
     }
     return f;
 }
@@ -185,14 +225,18 @@ __device__ __forceinline__ FaSummary fa_unpack(const uint4 v) {
     return f;
 }
 
-__global__ void __launch_bounds__(FA_THREADS) fasta_summarize_kernel(const unsigned char *__restrict__ text, u64 n, FaSummary *__restrict__ tiles,
+__global__ void __launch_bounds__(FA_THREADS, 2) fasta_summarize_kernel(const unsigned char *__restrict__ text, u64 n, FaSummary *__restrict__ tiles,
                                                                      uint4 *__restrict__ chunks) {
     typedef cub::BlockScan<FaSummary, FA_THREADS> Scan;
     __shared__ typename Scan::TempStorage tmp;
+    __shared__ u32 lut[256];
+    fa_init_lut(lut);
     const u64 beg = (u64)blockIdx.x * FA_TILE + (u64)threadIdx.x * FA_CHUNK;
     FaChunkBytes B;
     fa_load_chunk(text, beg, n, (reinterpret_cast<uintptr_t>(text) & 15) == 0, B);
-    FaSummary mine = fa_chunk_summary(B, beg, n), incl;
+    __syncthreads();
+    const FaChunkMasks C = fa_classify(B, lut);
+    FaSummary mine = fa_chunk_summary(C, beg, n), incl;
     chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x] = fa_pack(mine);
     Scan(tmp).InclusiveScan(mine, incl, FaCompose());
     if (threadIdx.x == FA_THREADS - 1) tiles[blockIdx.x] = incl;
@@ -202,17 +246,53 @@ __global__ void __launch_bounds__(FA_THREADS) fasta_summarize_kernel(const unsig
 struct FaTileEntry {
     u32 state, base0, run0, pad;
 };
+__device__ __forceinline__ FaSummary fa_shfl_up(const FaSummary &f, int d) {
+    FaSummary r;
+    r.exits = __shfl_up_sync(0xffffffffu, f.exits, d);
+#pragma unroll
+    for (int s = 0; s < 5; s++) {
+        r.nb[s] = __shfl_up_sync(0xffffffffu, f.nb[s], d);
+        r.nr[s] = __shfl_up_sync(0xffffffffu, f.nr[s], d);
+    }
+    return r;
+}
+// exclusive scan of one summary per thread over a CTA of 1024 threads (warp shuffles, then the 32 warp totals)
+__device__ __forceinline__ FaSummary fa_block_exclusive_scan(const FaSummary &mine, FaSummary *warp_tot /* [32] shared */) {
+    FaCompose op;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    FaSummary incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const FaSummary o = fa_shfl_up(incl, d);
+        if (lane >= d) incl = op(o, incl);
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        FaSummary t = warp_tot[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const FaSummary o = fa_shfl_up(t, d);
+            if (lane >= d) t = op(o, t);
+        }
+        const FaSummary ex = fa_shfl_up(t, 1);
+        warp_tot[lane] = lane == 0 ? fa_identity() : ex;  // exclusive prefix of the warps
+    }
+    __syncthreads();
+    const FaSummary prev = fa_shfl_up(incl, 1);
+    const FaSummary within = lane == 0 ? fa_identity() : prev;
+    return op(warp_tot[w], within);
+}
+
 __global__ void __launch_bounds__(1024) fasta_tiles_kernel(const FaSummary *__restrict__ tiles, u32 n_tiles, FaTileEntry *__restrict__ entry,
                                                            u64 *__restrict__ totals, u64 *__restrict__ offsets) {
-    typedef cub::BlockScan<FaSummary, 1024> Scan;
-    __shared__ typename Scan::TempStorage tmp;
+    __shared__ FaSummary warp_tot[32];
     const u32 per = (n_tiles + 1023) / 1024;
-    const u32 t0 = threadIdx.x * per, t1 = min(n_tiles, t0 + per);
+    const u32 t0 = min(n_tiles, threadIdx.x * per), t1 = min(n_tiles, t0 + per);
     FaSummary seg = fa_identity();
     FaCompose op;
     for (u32 t = t0; t < t1; t++) seg = op(seg, tiles[t]);
-    FaSummary before;
-    Scan(tmp).ExclusiveScan(seg, before, fa_identity(), op);
+    const FaSummary before = fa_block_exclusive_scan(seg, warp_tot);
     // walk the segment again from the state this thread's segment is entered in
     u32 state = before.exit_of(FA_H), base0 = before.nb[FA_H], run0 = before.nr[FA_H];
     for (u32 t = t0; t < t1; t++) {
@@ -235,38 +315,48 @@ __global__ void __launch_bounds__(1024) fasta_tiles_kernel(const FaSummary *__re
 // about 128 bytes apart) on different banks
 __device__ __forceinline__ u32 fa_stage_at(u32 off) { return off + ((off >> 7) << 2); }
 
-__global__ void __launch_bounds__(FA_THREADS) fasta_emit_kernel(const unsigned char *__restrict__ text, u64 n, const FaTileEntry *__restrict__ entry,
+__global__ void __launch_bounds__(FA_THREADS, 2) fasta_emit_kernel(const unsigned char *__restrict__ text, u64 n, const FaTileEntry *__restrict__ entry,
                                                                 const uint4 *__restrict__ chunks, unsigned char *__restrict__ bases,
                                                                 u64 *__restrict__ offsets) {
     typedef cub::BlockScan<FaSummary, FA_THREADS> Scan;
     __shared__ typename Scan::TempStorage tmp;
     __shared__ unsigned char stage[FA_TILE + (FA_TILE >> 7) * 4 + 16];
     __shared__ u32 s_total;
+    __shared__ u32 lut[256];
+    fa_init_lut(lut);
     const u64 beg = (u64)blockIdx.x * FA_TILE + (u64)threadIdx.x * FA_CHUNK;
     FaSummary mine = fa_unpack(chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x]), before;
     Scan(tmp).ExclusiveScan(mine, before, fa_identity(), FaCompose());
     const FaTileEntry e = entry[blockIdx.x];
-    u32 state = before.exit_of(e.state);
+    const u32 state = before.exit_of(e.state);
     u32 lb = fa_pick(before.nb, e.state);  // index of this thread's first base inside the tile's output
     u64 r = (u64)e.run0 + fa_pick(before.nr, e.state);
     if (threadIdx.x == FA_THREADS - 1) s_total = lb + fa_pick(mine.nb, state);
     FaChunkBytes B;
     fa_load_chunk(text, beg, n, (reinterpret_cast<uintptr_t>(text) & 15) == 0, B);
+    __syncthreads();  // lut
     const int len = beg >= n ? 0 : (n - beg < FA_CHUNK ? (int)(n - beg) : FA_CHUNK);
+    const FaChunkMasks C = fa_classify(B, lut);
+    M128 K, St;
+    fa_masks(C, len, state, K, St);
+    // one offset per run that starts in the chunk: the number of emitted bases before it
+    for (int half = 0; half < 2; half++) {
+        u64 sm = half ? St.hi : St.lo;
+        while (sm) {
+            const int p = __ffsll((long long)sm) - 1;
+            sm &= sm - 1;
+            const u32 before_p = half ? __popcll(K.lo) + __popcll(K.hi & ((1ull << p) - 1)) : __popcll(K.lo & ((1ull << p) - 1));
+            offsets[r++] = (u64)e.base0 + lb + before_p;
+        }
+    }
+    // the emitted bytes, upper-cased, into the tile's staging area
 #pragma unroll
     for (int i = 0; i < FA_CHUNK / 16; i++) {
+        const u32 w[4] = {B.q[i].x, B.q[i].y, B.q[i].z, B.q[i].w};
+        const u32 k16 = (u32)((i < 4 ? K.lo >> (16 * i) : K.hi >> (16 * (i - 4))) & 0xffffu);
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-            if (16 * i + j < len) {
-                const unsigned char c = fa_byte(B, i, j);
-                const u32 cls = fasta_class(c);
-                bool em, st;
-                state = fasta_step(state, cls, fasta_map(cls), em, st);
-                if (em) {
-                    if (st) offsets[r++] = (u64)e.base0 + lb;
-                    stage[fa_stage_at(lb++)] = c & 0xDF;
-                }
-            }
+            if ((k16 >> j) & 1u) stage[fa_stage_at(lb++)] = (unsigned char)((w[j >> 2] >> (8 * (j & 3))) & 0xDFu);
         }
     }
     __syncthreads();
