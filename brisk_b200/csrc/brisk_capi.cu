@@ -2101,6 +2101,38 @@ extern "C" int brisk_parse_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     return BRISK_OK;
 }
 
+// A text of any size is handed to the parser in pieces of about 1 GB that end right before a header line ("\n>"): every
+// piece starts with a header like a file does, so the pieces parse independently and no read spans two of them (the
+// 32-bit positions of the tile scan cap one parse at 4 GB; the pieces also bound the scratch memory of a call).
+static int fasta_pieces(brisk_handle *h, const char *text, uint64_t n, std::vector<std::pair<uint64_t, uint64_t>> &pieces) {
+    const uint64_t target = 1ull << 30, window = 4ull << 20;
+    const bool dev = is_device_ptr(text);
+    std::vector<char> buf;
+    uint64_t at = 0;
+    while (n - at > target + target / 2) {
+        // the last "\n>" at or before at + target, looked for in growing windows
+        uint64_t cut = 0;
+        for (uint64_t back = window; cut == 0; back *= 4) {
+            const uint64_t hi = at + target, lo = hi > at + back ? hi - back : at + 1;
+            const char *w = text + lo;
+            if (dev) {
+                buf.resize(hi - lo + 1);
+                CK(cudaMemcpy(buf.data(), text + lo, hi - lo + 1, cudaMemcpyDeviceToHost));
+                w = buf.data();
+            }
+            for (uint64_t i = hi - lo; i >= 1; i--)
+                if (w[i] == '>' && w[i - 1] == '\n') { cut = lo + i; break; }
+            if (lo == at + 1) break;
+        }
+        if (cut == 0) return fail(BRISK_E_PARAM, "FASTA text: no record boundary within 1 GB (one record of more than 1 GB is not supported)");
+        pieces.push_back({at, cut - at});
+        at = cut;
+    }
+    pieces.push_back({at, n - at});
+    (void)h;
+    return BRISK_OK;
+}
+
 // count_fasta / query_fasta of the demo app (apps/counter.cpp:197-226, :314-345) for one text buffer
 extern "C" int brisk_count_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *n_reads_out) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
@@ -2108,11 +2140,20 @@ extern "C" int brisk_count_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     SETTLE_PENDING(h);
-    uint64_t nb = 0, nr = 0;
-    int rc = parse_fasta(h, text, n_bytes, nb, nr);
+    std::vector<std::pair<uint64_t, uint64_t>> pieces;
+    int rc = fasta_pieces(h, text, n_bytes, pieces);
     if (rc) return rc;
-    if (n_reads_out) *n_reads_out = nr;
-    return brisk_count_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr);
+    uint64_t reads = 0;
+    for (auto &pc : pieces) {
+        uint64_t nb = 0, nr = 0;
+        rc = parse_fasta(h, text + pc.first, pc.second, nb, nr);
+        if (rc) return rc;
+        reads += nr;
+        rc = brisk_count_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr);
+        if (rc) return rc;
+    }
+    if (n_reads_out) *n_reads_out = reads;
+    return BRISK_OK;
 }
 extern "C" int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes, uint64_t *hits, uint64_t *total) {
     if (!h) return fail(BRISK_E_PARAM, "null handle");
@@ -2120,10 +2161,21 @@ extern "C" int brisk_query_fasta(brisk_t *h, const char *text, uint64_t n_bytes,
     std::lock_guard<std::recursive_mutex> lock(h->mu);
     CK(cudaSetDevice(h->device));
     SETTLE_PENDING(h);
-    uint64_t nb = 0, nr = 0;
-    int rc = parse_fasta(h, text, n_bytes, nb, nr);
+    std::vector<std::pair<uint64_t, uint64_t>> pieces;
+    int rc = fasta_pieces(h, text, n_bytes, pieces);
     if (rc) return rc;
-    return brisk_query_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr, hits, total);
+    uint64_t H = 0, T = 0;
+    for (auto &pc : pieces) {
+        uint64_t nb = 0, nr = 0, h1 = 0, t1 = 0;
+        rc = parse_fasta(h, text + pc.first, pc.second, nb, nr);
+        if (rc) return rc;
+        rc = brisk_query_reads(h, (const char *)h->d_fa_bases.p, (const uint64_t *)h->d_fa_offsets.p, nr, &h1, &t1);
+        if (rc) return rc;
+        H += h1; T += t1;
+    }
+    if (hits) *hits = H;
+    if (total) *total = T;
+    return BRISK_OK;
 }
 
 // ---- partition and record-level entry points (what a rank does before and after the exchange)

@@ -20,8 +20,6 @@
 // The text is read twice, the bases written once, a 16-byte summary per 128-byte chunk written and read back:
 // about 3.3 bytes of HBM traffic per text byte.
 #pragma once
-#include <cub/block/block_scan.cuh>
-
 #include "common.cuh"
 
 #define FA_THREADS 256
@@ -225,27 +223,6 @@ __device__ __forceinline__ FaSummary fa_unpack(const uint4 v) {
     return f;
 }
 
-__global__ void __launch_bounds__(FA_THREADS, 2) fasta_summarize_kernel(const unsigned char *__restrict__ text, u64 n, FaSummary *__restrict__ tiles,
-                                                                     uint4 *__restrict__ chunks) {
-    typedef cub::BlockScan<FaSummary, FA_THREADS> Scan;
-    __shared__ typename Scan::TempStorage tmp;
-    __shared__ u32 lut[256];
-    fa_init_lut(lut);
-    const u64 beg = (u64)blockIdx.x * FA_TILE + (u64)threadIdx.x * FA_CHUNK;
-    FaChunkBytes B;
-    fa_load_chunk(text, beg, n, (reinterpret_cast<uintptr_t>(text) & 15) == 0, B);
-    __syncthreads();
-    const FaChunkMasks C = fa_classify(B, lut);
-    FaSummary mine = fa_chunk_summary(C, beg, n), incl;
-    chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x] = fa_pack(mine);
-    Scan(tmp).InclusiveScan(mine, incl, FaCompose());
-    if (threadIdx.x == FA_THREADS - 1) tiles[blockIdx.x] = incl;
-}
-
-// per tile: entry state | first base index | first run index, from the start state H (the first line is a header)
-struct FaTileEntry {
-    u32 state, base0, run0, pad;
-};
 __device__ __forceinline__ FaSummary fa_shfl_up(const FaSummary &f, int d) {
     FaSummary r;
     r.exits = __shfl_up_sync(0xffffffffu, f.exits, d);
@@ -256,8 +233,10 @@ __device__ __forceinline__ FaSummary fa_shfl_up(const FaSummary &f, int d) {
     }
     return r;
 }
-// exclusive scan of one summary per thread over a CTA of 1024 threads (warp shuffles, then the 32 warp totals)
-__device__ __forceinline__ FaSummary fa_block_exclusive_scan(const FaSummary &mine, FaSummary *warp_tot /* [32] shared */) {
+// exclusive scan of one summary per thread over a CTA of NW warps (warp shuffles, then the NW warp totals); *total
+// (optional) receives the composition of the whole CTA
+template <int NW>
+__device__ __forceinline__ FaSummary fa_block_exclusive_scan(const FaSummary &mine, FaSummary *warp_tot /* [32] shared */, FaSummary *total = nullptr) {
     FaCompose op;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     FaSummary incl = mine;
@@ -269,30 +248,66 @@ __device__ __forceinline__ FaSummary fa_block_exclusive_scan(const FaSummary &mi
     if (lane == 31) warp_tot[w] = incl;
     __syncthreads();
     if (w == 0) {
-        FaSummary t = warp_tot[lane];
+        FaSummary t = lane < NW ? warp_tot[lane] : fa_identity();
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
+        for (int d = 1; d < NW; d <<= 1) {
             const FaSummary o = fa_shfl_up(t, d);
             if (lane >= d) t = op(o, t);
         }
         const FaSummary ex = fa_shfl_up(t, 1);
-        warp_tot[lane] = lane == 0 ? fa_identity() : ex;  // exclusive prefix of the warps
+        if (lane < NW) warp_tot[lane] = lane == 0 ? fa_identity() : ex;  // exclusive prefix of the warps
+        if (lane == NW - 1) warp_tot[NW] = t;                             // everything
     }
     __syncthreads();
+    if (total) *total = warp_tot[NW];
     const FaSummary prev = fa_shfl_up(incl, 1);
     const FaSummary within = lane == 0 ? fa_identity() : prev;
     return op(warp_tot[w], within);
 }
 
+__global__ void __launch_bounds__(FA_THREADS, 2) fasta_summarize_kernel(const unsigned char *__restrict__ text, u64 n, FaSummary *__restrict__ tiles,
+                                                                     uint4 *__restrict__ chunks) {
+    __shared__ FaSummary warp_tot[FA_THREADS / 32 + 1];
+    __shared__ u32 lut[256];
+    fa_init_lut(lut);
+    const u64 beg = (u64)blockIdx.x * FA_TILE + (u64)threadIdx.x * FA_CHUNK;
+    FaChunkBytes B;
+    fa_load_chunk(text, beg, n, (reinterpret_cast<uintptr_t>(text) & 15) == 0, B);
+    __syncthreads();
+    const FaChunkMasks C = fa_classify(B, lut);
+    const FaSummary mine = fa_chunk_summary(C, beg, n);
+    chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x] = fa_pack(mine);
+    // the tile's summary = the composition of its 256 chunks: warp totals only (no per-thread prefix is needed here)
+    FaCompose op;
+    FaSummary incl = mine;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const FaSummary o = fa_shfl_up(incl, d);
+        if (lane >= d) incl = op(o, incl);
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        FaSummary t = warp_tot[0];
+        for (int i = 1; i < FA_THREADS / 32; i++) t = op(t, warp_tot[i]);
+        tiles[blockIdx.x] = t;
+    }
+}
+
+// per tile: entry state | first base index | first run index, from the start state H (the first line is a header)
+struct FaTileEntry {
+    u32 state, base0, run0, pad;
+};
 __global__ void __launch_bounds__(1024) fasta_tiles_kernel(const FaSummary *__restrict__ tiles, u32 n_tiles, FaTileEntry *__restrict__ entry,
                                                            u64 *__restrict__ totals, u64 *__restrict__ offsets) {
-    __shared__ FaSummary warp_tot[32];
+    __shared__ FaSummary warp_tot[33];
     const u32 per = (n_tiles + 1023) / 1024;
     const u32 t0 = min(n_tiles, threadIdx.x * per), t1 = min(n_tiles, t0 + per);
     FaSummary seg = fa_identity();
     FaCompose op;
     for (u32 t = t0; t < t1; t++) seg = op(seg, tiles[t]);
-    const FaSummary before = fa_block_exclusive_scan(seg, warp_tot);
+    const FaSummary before = fa_block_exclusive_scan<32>(seg, warp_tot);
     // walk the segment again from the state this thread's segment is entered in
     u32 state = before.exit_of(FA_H), base0 = before.nb[FA_H], run0 = before.nr[FA_H];
     for (u32 t = t0; t < t1; t++) {
@@ -318,15 +333,14 @@ __device__ __forceinline__ u32 fa_stage_at(u32 off) { return off + ((off >> 7) <
 __global__ void __launch_bounds__(FA_THREADS, 2) fasta_emit_kernel(const unsigned char *__restrict__ text, u64 n, const FaTileEntry *__restrict__ entry,
                                                                 const uint4 *__restrict__ chunks, unsigned char *__restrict__ bases,
                                                                 u64 *__restrict__ offsets) {
-    typedef cub::BlockScan<FaSummary, FA_THREADS> Scan;
-    __shared__ typename Scan::TempStorage tmp;
+    __shared__ FaSummary warp_tot[FA_THREADS / 32 + 1];
     __shared__ unsigned char stage[FA_TILE + (FA_TILE >> 7) * 4 + 16];
     __shared__ u32 s_total;
     __shared__ u32 lut[256];
     fa_init_lut(lut);
     const u64 beg = (u64)blockIdx.x * FA_TILE + (u64)threadIdx.x * FA_CHUNK;
-    FaSummary mine = fa_unpack(chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x]), before;
-    Scan(tmp).ExclusiveScan(mine, before, fa_identity(), FaCompose());
+    const FaSummary mine = fa_unpack(chunks[(u64)blockIdx.x * FA_THREADS + threadIdx.x]);
+    const FaSummary before = fa_block_exclusive_scan<FA_THREADS / 32>(mine, warp_tot);
     const FaTileEntry e = entry[blockIdx.x];
     const u32 state = before.exit_of(e.state);
     u32 lb = fa_pick(before.nb, e.state);  // index of this thread's first base inside the tile's output

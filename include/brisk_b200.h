@@ -182,7 +182,8 @@ int brisk_last_timing(brisk_t *h, float ms[5], uint32_t *n_launches);
 /* ---- FASTA ingest on the device: what getLineFasta + clean_dna (apps/counter.cpp:128-190) hand to count_sequence
  * with one reader thread — per record (first line of the text or any line starting with '>' = header) the maximal runs
  * of [ACGTacgt] of its concatenated lines, upper-cased, in file order.  `text` (host or device) must hold whole
- * records and be shorter than 2^32 - 2 bytes; split big files at a record boundary.
+ * records.  brisk_parse_fasta takes texts shorter than 2^32 - 2 bytes; brisk_count_fasta / brisk_query_fasta take
+ * texts of any size (they walk them in pieces of about 1 GB cut right before a header line).
  * brisk_parse_fasta: the reads as a flat buffer + n_reads + 1 offsets (outputs nullable to only count);
  * brisk_count_fasta / brisk_query_fasta: count_fasta (apps/counter.cpp:197-226) / query_fasta (:314-345). */
 int brisk_parse_fasta(brisk_t *h, const char *text, uint64_t n_bytes, char *bases, uint64_t cap_bases, uint64_t *offsets,
