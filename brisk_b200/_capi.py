@@ -45,6 +45,7 @@ PROTOTYPES = {
     "brisk_reparameterise": (C.c_int, [C.c_void_p, C.c_uint8, C.c_uint8]),
     "brisk_long_read_info": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brisk_checksum": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "brisk_checksum_kmers_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_synth_genome": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]),
     "brisk_synth_reads": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brisk_decycle_tables": (C.c_int, [C.c_uint8, C.c_uint8, C.c_uint8, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -2334,3 +2334,121 @@ extern "C" int brisk_comm_info(brisk_t *h, int *rank, int *n_ranks) {
     if (n_ranks) *n_ranks = h->comm ? h->comm->n : 1;
     return BRISK_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// brisk_checksum_kmers_noalloc — the checksum of brisk_checksum over an explicit list of (k-mer, DATA byte) pairs (a
+// dump), for callers that must not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// The scratch (a ticket + one partial triple per CTA) is a file-scope
+// __device__ array: every GPU that loads the library holds its 384.25 KiB until exit.  Nothing here calls cudaMalloc,
+// cudaFree or any allocating routine.  All calls share the array: calls that overlap on one GPU race.
+#define NOALLOC_TILE 4096u                        // k-mers per CTA (256 threads x 16)
+#define NOALLOC_MAX_CTAS 16384u                   // => at most 2^26 k-mers per call (BRISK_NOALLOC_MAX_KMERS)
+#define NOALLOC_HEAD 32u                          // u64 words before the partials; word 0 = ticket
+static_assert((uint64_t)NOALLOC_TILE * NOALLOC_MAX_CTAS == BRISK_NOALLOC_MAX_KMERS, "header and kernel disagree on the limit");
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_HEAD + 3 * NOALLOC_MAX_CTAS];
+
+// sums a, b, c over the CTA; the result is valid in thread 0
+__device__ __forceinline__ void noalloc_block_sum(u64 &a, u64 &b, u64 &c, u64 (*sh)[3]) {
+    for (int d = 16; d > 0; d >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, d);
+        b += __shfl_xor_sync(0xffffffffu, b, d);
+        c += __shfl_xor_sync(0xffffffffu, c, d);
+    }
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { sh[w][0] = a; sh[w][1] = b; sh[w][2] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = b = c = 0;
+        for (int i = 0; i < 8; i++) { a += sh[i][0]; b += sh[i][1]; c += sh[i][2]; }
+    }
+    __syncthreads();
+}
+
+// keys as u64 triples {lo, hi, idx | pad << 8} (brisk_kmer); every CTA leaves its partial sums in the scratch, the CTA
+// that takes the last ticket adds them up and writes out[0..2]
+__global__ void __launch_bounds__(256) checksum_kmers_noalloc_kernel(const u64 *__restrict__ keys, const unsigned char *__restrict__ data,
+                                                                     u64 n, u64 *scratch, u64 *out) {
+    __shared__ u64 sh[8][3];
+    __shared__ bool last;
+    u64 *part = scratch + NOALLOC_HEAD;
+    u64 a = 0, b = 0, c = 0;
+    const u64 base = (u64)blockIdx.x * NOALLOC_TILE;
+#pragma unroll 4
+    for (u32 r = 0; r < NOALLOC_TILE / 256; r++) {
+        const u64 i = base + (u64)r * 256 + threadIdx.x;
+        if (i < n) {
+            const u64 lo = keys[3 * i], hi = keys[3 * i + 1];
+            const u32 idx = (u32)(keys[3 * i + 2] & 0xffu), d = data[i];
+            a += checksum_mix(lo, hi, idx, d);
+            b += d;
+            c += 1;
+        }
+    }
+    noalloc_block_sum(a, b, c, sh);
+    if (threadIdx.x == 0) {
+        part[3 * (u64)blockIdx.x] = a;
+        part[3 * (u64)blockIdx.x + 1] = b;
+        part[3 * (u64)blockIdx.x + 2] = c;
+        __threadfence();
+        last = atomicAdd((unsigned long long *)scratch, 1ull) == (unsigned long long)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    a = b = c = 0;
+    for (u32 i = threadIdx.x; i < gridDim.x; i += 256) {
+        a += __ldcg(part + 3 * (u64)i);
+        b += __ldcg(part + 3 * (u64)i + 1);
+        c += __ldcg(part + 3 * (u64)i + 2);
+    }
+    noalloc_block_sum(a, b, c, sh);
+    if (threadIdx.x == 0) { out[0] = a; out[1] = b; out[2] = c; }
+}
+
+// once per device, with that device current: the DEVICE address of g_noalloc_scratch (its name in host code is only a
+// host-side stand-in for the symbol)
+static int noalloc_scratch_of_current_device(int dev, u64 **ptr) {
+    static std::mutex mu;
+    static u64 *addr[64] = {};
+    if (dev < 0 || dev >= 64) return fail(BRISK_E_PARAM, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail(BRISK_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        addr[dev] = (u64 *)p;
+    }
+    *ptr = addr[dev];
+    return BRISK_OK;
+}
+
+extern "C" int brisk_checksum_kmers_noalloc(const brisk_kmer *keys, const uint8_t *data, uint64_t n, uint64_t *out, void *stream) {
+    if (!out) return fail(BRISK_E_PARAM, "null output");
+    if (n && (!keys || !data)) return fail(BRISK_E_PARAM, "null input");
+    if (n > BRISK_NOALLOC_MAX_KMERS)
+        return fail(BRISK_E_CAPACITY, "brisk_checksum_kmers_noalloc: " + std::to_string(n) + " k-mers exceed the static scratch's limit of " +
+                                          std::to_string((uint64_t)BRISK_NOALLOC_MAX_KMERS) + " per call (split the list and add the sums)");
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    const void *ptrs[3] = {out, n ? (const void *)keys : nullptr, n ? (const void *)data : nullptr};
+    for (int i = 0; i < 3; i++) {
+        if (!ptrs[i]) continue;
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, ptrs[i]) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
+            cudaGetLastError();
+            return fail(BRISK_E_PARAM, "keys, data and out must be device pointers");
+        }
+        if (at.device != dev) return fail(BRISK_E_PARAM, "keys, data and out must live on the current device");
+    }
+    if ((uintptr_t)keys & 7u || (uintptr_t)out & 7u) return fail(BRISK_E_PARAM, "keys and out must be 8-byte aligned");
+    u64 *scratch = nullptr;
+    int rc = noalloc_scratch_of_current_device(dev, &scratch);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    // the array keeps the last call's contents: the ticket must start at zero (the partials are overwritten before use)
+    CK(cudaMemsetAsync(scratch, 0, sizeof(u64), s));
+    const unsigned ctas = n ? (unsigned)((n + NOALLOC_TILE - 1) / NOALLOC_TILE) : 1u;
+    checksum_kmers_noalloc_kernel<<<ctas, 256, 0, s>>>((const u64 *)keys, data, n, scratch, (u64 *)out);
+    CK(cudaGetLastError());
+    return BRISK_OK;
+}

@@ -146,6 +146,19 @@ int brisk_stats(brisk_t *h, uint64_t *nb_buckets, uint64_t *nb_skmers, uint64_t 
  * stored k-mers.  The sums over the shards equal the sums of an unsharded index over the same reads. */
 int brisk_checksum(brisk_t *h, uint64_t out[3]);
 
+/* brisk_checksum's three sums over an explicit list of k-mers and their DATA bytes (what brisk_dump returns): equal to
+ * brisk_checksum of the handle the list was dumped from; the sums of several lists add up.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot allocate (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  The call allocates nothing: its scratch is a static __device__
+ * array of 384.25 KiB that every GPU loading the library holds until exit, which limits one call to
+ * BRISK_NOALLOC_MAX_KMERS k-mers (more: BRISK_E_CAPACITY; split the list and add the sums).  keys, data (1 byte per
+ * k-mer) and out (3 x uint64) are DEVICE pointers on the current device; the work is queued on `stream` (cudaStream_t,
+ * NULL = default stream) and not waited for.  All calls on a GPU share the scratch: calls that may overlap on the GPU
+ * (different streams without an ordering between them) race; calls on one stream are safe back to back.  The first
+ * call on a device resolves the scratch's address (cudaGetSymbolAddress): make it before a graph capture starts. */
+#define BRISK_NOALLOC_MAX_KMERS (1ull << 26)
+int brisk_checksum_kmers_noalloc(const brisk_kmer *keys, const uint8_t *data, uint64_t n, uint64_t *out, void *stream);
+
 /* benchmark / test support: the synthetic generator of brisk_b200/synth.py on the device,
  * bit-identical to it.  genome / out are device pointers on the current device, stream a cudaStream_t (NULL = default
  * stream); the kernels are queued, not waited for.  Reads first .. first+count-1 of the set, L bytes each. */
