@@ -75,6 +75,8 @@ struct brisk_handle {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t chunk_ev[BRISK_MAX_CHUNKS] = {};
     cudaEvent_t offsets_ev = nullptr;
+    cudaStream_t store_stream = nullptr;  // run_reads_overlapped: the store kernel of a batch's first chunks (low priority)
+    cudaEvent_t ov_ev[2] = {};            // [0] the handle's stream is ready for that kernel, [1] the kernel is done
     bool pending_settle = false;  // a count / insert call left its store kernel running: settle() before the table is used again
     bool timing_dirty = false;    // stage times of the last call not read back yet
     float last_ms[5] = {0, 0, 0, 0, 0};
@@ -383,6 +385,8 @@ extern "C" int brisk_destroy(brisk_t *h) {
     for (int i = 0; i < BRISK_MAX_CHUNKS; i++) cudaEventDestroy(h->chunk_ev[i]);
     if (h->offsets_ev) cudaEventDestroy(h->offsets_ev);
     cudaStreamDestroy(h->copy_stream);
+    if (h->store_stream) cudaStreamDestroy(h->store_stream);
+    for (int i = 0; i < 2; i++) if (h->ov_ev[i]) cudaEventDestroy(h->ov_ev[i]);
     cudaStreamDestroy(h->own_stream);
     delete h;
     return BRISK_OK;
@@ -690,7 +694,7 @@ static int enumerate_batch(brisk_handle *h, const ReadBatch &B, bool with_occ, u
 }
 
 template <int RW, int KW, int MODE>
-static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n_recs, OccOut O) {
+static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n_recs, OccOut O, cudaStream_t st, int ctas_per_sm) {
     if (n_recs == 0) return cudaSuccess;
     uint64_t want = (n_recs + 255) / 256;  // one warp per 32 records
     // persistent grid: exactly the CTAs that are resident at once (B200: 148 SMs), every warp strides over the records
@@ -701,28 +705,29 @@ static cudaError_t launch_records_t(brisk_handle *h, const u64 *recs, uint64_t n
         if (const char *e = getenv("BRISK_STORE_CTAS")) v = std::max(1, atoi(e));
         per_sm = v;
     }
-    unsigned blocks = (unsigned)std::min<uint64_t>(want, (uint64_t)148 * per_sm);
-    records_kernel<RW, KW, MODE><<<blocks, 256, 0, h->stream>>>(h->P, recs, n_recs, view_of(h), O);
+    unsigned blocks = (unsigned)std::min<uint64_t>(want, (uint64_t)148 * (ctas_per_sm > 0 ? std::min(ctas_per_sm, per_sm) : per_sm));
+    records_kernel<RW, KW, MODE><<<blocks, 256, 0, st ? st : h->stream>>>(h->P, recs, n_recs, view_of(h), O);
     return cudaGetLastError();
 }
 template <int RW, int KW>
-static cudaError_t launch_records_m(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O) {
+static cudaError_t launch_records_m(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O, cudaStream_t st, int ctas_per_sm) {
     switch (mode) {
-        case MODE_COUNT: return launch_records_t<RW, KW, MODE_COUNT>(h, recs, n_recs, O);
-        case MODE_INSERT: return launch_records_t<RW, KW, MODE_INSERT>(h, recs, n_recs, O);
-        default: return launch_records_t<RW, KW, MODE_GET>(h, recs, n_recs, O);
+        case MODE_COUNT: return launch_records_t<RW, KW, MODE_COUNT>(h, recs, n_recs, O, st, ctas_per_sm);
+        case MODE_INSERT: return launch_records_t<RW, KW, MODE_INSERT>(h, recs, n_recs, O, st, ctas_per_sm);
+        default: return launch_records_t<RW, KW, MODE_GET>(h, recs, n_recs, O, st, ctas_per_sm);
     }
 }
-static cudaError_t launch_records(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O) {
+// st = nullptr: the handle's stream; ctas_per_sm > 0 caps the persistent grid's residency
+static cudaError_t launch_records(brisk_handle *h, int mode, const u64 *recs, uint64_t n_recs, OccOut O, cudaStream_t st = nullptr, int ctas_per_sm = 0) {
     const int RW = h->P.rec_words, KW = h->P.key_words;
     if (KW == 1) {
-        if (RW == 2) return launch_records_m<2, 1>(h, mode, recs, n_recs, O);
-        if (RW == 4) return launch_records_m<4, 1>(h, mode, recs, n_recs, O);
-        return launch_records_m<6, 1>(h, mode, recs, n_recs, O);
+        if (RW == 2) return launch_records_m<2, 1>(h, mode, recs, n_recs, O, st, ctas_per_sm);
+        if (RW == 4) return launch_records_m<4, 1>(h, mode, recs, n_recs, O, st, ctas_per_sm);
+        return launch_records_m<6, 1>(h, mode, recs, n_recs, O, st, ctas_per_sm);
     }
-    if (RW == 2) return launch_records_m<2, 2>(h, mode, recs, n_recs, O);
-    if (RW == 4) return launch_records_m<4, 2>(h, mode, recs, n_recs, O);
-    return launch_records_m<6, 2>(h, mode, recs, n_recs, O);
+    if (RW == 2) return launch_records_m<2, 2>(h, mode, recs, n_recs, O, st, ctas_per_sm);
+    if (RW == 4) return launch_records_m<4, 2>(h, mode, recs, n_recs, O, st, ctas_per_sm);
+    return launch_records_m<6, 2>(h, mode, recs, n_recs, O, st, ctas_per_sm);
 }
 
 // ------------------------------------------------------------------------------------------------ partition / exchange
@@ -1191,6 +1196,156 @@ static void finish_timing(brisk_handle *h) {
     cudaEventElapsedTime(&h->last_ms[4], h->ev[0], h->ev[4]);
 }
 
+// Host input with nothing to hand back per occurrence (brisk_count_reads, brisk_query_reads, brisk_insert_reads without
+// outputs) on an unsharded index: the batch arrives in chunks over PCIe for about as long as all its kernels take, so
+// the chunks are cut into GROUPS, and the records of every group but the last go to the store kernel WHILE the later
+// chunks are still on their way — on a second, low-priority stream with a capped residency, so that pack + enumerate
+// of the arriving chunks are not queued behind it.  What is left after the last byte has arrived is the enumeration
+// of the last chunk and the store kernel over the last group only.  Each group enumerates into its own region of
+// d_recs and is put in table-region order on its own (d_send, same regions).  done = false: nothing has been applied
+// (the first group's region was too small) and the caller runs the plain path.
+static std::vector<size_t> overlap_cuts(const char *env_name, const char *dflt) {
+    const char *e = getenv(env_name);
+    std::vector<size_t> v;
+    for (const char *p = e ? e : dflt; *p;) {
+        char *end = nullptr;
+        const long x = strtol(p, &end, 10);
+        if (end == p) break;
+        if (x > 0 && (v.empty() || (size_t)x > v.back())) v.push_back((size_t)x);
+        p = *end ? end + 1 : end;
+    }
+    return v;
+}
+static int run_reads_overlapped(brisk_handle *h, const ReadBatch &B, int mode, OccOut O, bool &done) {
+    done = false;
+    // development switches: the chunk indices (of 8) at which a new group starts, "0" = off; the residency cap of the
+    // store kernels that run beside the enumeration; 0 = everything on the handle's stream
+    static const std::vector<size_t> cuts_put = overlap_cuts("BRISK_OVERLAP_COUNT", "3"), cuts_get = overlap_cuts("BRISK_OVERLAP_GET", "3");
+    static const int ctas_env = getenv("BRISK_OVERLAP_CTAS") ? atoi(getenv("BRISK_OVERLAP_CTAS")) : 2;
+    static const int stream_env = getenv("BRISK_OVERLAP_STREAM") ? atoi(getenv("BRISK_OVERLAP_STREAM")) : 1;
+    const size_t nc = B.chunk_first.size() - 1;
+    std::vector<size_t> cut(1, 0);
+    for (size_t c : (mode == MODE_GET ? cuts_get : cuts_put)) if (c < nc) cut.push_back(c);
+    cut.push_back(nc);
+    const int ng = (int)cut.size() - 1;
+    if (ng < 2 || nc < 4) return BRISK_OK;
+    const int RW = h->P.rec_words;
+    if (!h->store_stream) {
+        int lo_p = 0, hi_p = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
+        CK(cudaStreamCreateWithPriority(&h->store_stream, cudaStreamNonBlocking, lo_p));
+        for (int i = 0; i < 2; i++) CK(cudaEventCreateWithFlags(&h->ov_ev[i], cudaEventDisableTiming));
+    }
+    cudaStream_t side = stream_env ? h->store_stream : h->stream;
+    if (mode != MODE_GET) {  // room for the whole batch before its first store kernel (a rehash runs on the handle's stream)
+        const uint64_t lost = B.n_reads * (uint64_t)(h->P.k - 1);
+        int rc = pregrow(h, B.total_bytes > lost ? B.total_bytes - lost : B.total_bytes, false);
+        if (rc) return rc;
+    }
+    // record regions of the groups
+    std::vector<uint64_t> base(ng + 1, 0), ccap(ng, 0);
+    for (int g = 0; g < ng; g++) {
+        const uint64_t bytes = B.chunk_byte[cut[g + 1]] - B.chunk_byte[cut[g]], reads = B.chunk_first[cut[g + 1]] - B.chunk_first[cut[g]];
+        ccap[g] = std::min(bytes + 1, (uint64_t)(3.0 * (double)bytes / (h->P.w + 1)) + reads + 4096);
+    }
+    if (const char *tc = getenv("BRISK_OVERLAP_TEST_CAP")) {  // tests: "g:cap" makes group g's region too small
+        const int g = atoi(tc);
+        const char *colon = strchr(tc, ':');
+        if (colon && g >= 0 && g < ng) ccap[g] = std::min<uint64_t>(ccap[g], strtoull(colon + 1, nullptr, 10));
+    }
+    for (int g = 0; g < ng; g++) base[g + 1] = base[g] + ccap[g];
+    CK(h->d_recs.ensure((base[ng] + 1) * RW * sizeof(uint64_t)));
+    if (h->region_sort) CK(h->d_send.ensure((base[ng] + 1) * RW * sizeof(uint64_t)));
+    // every group counts behind d_rec_count[0] (where the long-read launch appends): the host waits for a group's
+    // enumeration before the next one is queued
+    EnumLong lg = no_long();
+    if (h->long_limit) {
+        CK(h->d_long.ensure((B.n_reads + 1) * sizeof(uint64_t)));
+        lg.list = (u64 *)h->d_long.p; lg.cap = B.n_reads; lg.count = (u64 *)h->d_rec_count + 8; lg.limit = h->long_limit;
+    }
+    // region order + store kernel of one group on stream st
+    auto store_group = [&](const u64 *recs, uint64_t n, u64 *sorted, cudaStream_t st, int ctas) -> int {
+        if (n == 0) return BRISK_OK;
+        if (!st) st = h->stream;
+        if (h->region_sort && n >= 4096) {
+            CK(cudaMemsetAsync(h->d_part2, 0, 64 * sizeof(uint64_t), st));
+            CK(RW == 2 ? launch_partition<2>(h, h->d_part2, recs, nullptr, n, STORE_REGIONS, 1, sorted, nullptr, st)
+                       : RW == 4 ? launch_partition<4>(h, h->d_part2, recs, nullptr, n, STORE_REGIONS, 1, sorted, nullptr, st)
+                                 : launch_partition<6>(h, h->d_part2, recs, nullptr, n, STORE_REGIONS, 1, sorted, nullptr, st));
+            h->last_launches += 3;
+            recs = sorted;
+        }
+        CK(launch_records(h, mode, recs, n, O, st, ctas));
+        h->last_launches++;
+        return BRISK_OK;
+    };
+    bool side_busy = false;  // store kernels of earlier groups may still be running on the side stream
+    for (int g = 0; g < ng; g++) {
+        const bool last = g + 1 == ng;
+        EnumOut out;
+        out.recs = (u64 *)h->d_recs.p + base[g] * RW;
+        out.rec_cap = ccap[g];
+        out.rec_count = (u64 *)h->d_rec_count;
+        out.rec_occ = nullptr;
+        out.kmer_base = nullptr;
+        CK(cudaMemsetAsync(h->d_rec_count, 0, 9 * sizeof(uint64_t), h->stream));  // record counter [0], long-read counter [8]
+        for (size_t c = cut[g]; c < cut[g + 1]; c++) {
+            int prc = pack_chunk(h, B, c);
+            if (prc) return prc;
+            if (c == 0) CK(cudaEventRecord(h->ev[1], h->stream));
+            const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
+            if (r1 == r0) continue;
+            CK(launch_enum(h, B, r0, r1, out, nullptr, lg));
+            h->last_launches++;
+        }
+        uint64_t n = 0, n_long = 0;
+        CK(cudaMemcpyAsync(&n, h->d_rec_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        if (lg.list) CK(cudaMemcpyAsync(&n_long, lg.count, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        if (n_long && n <= ccap[g]) {  // reads beyond the thread-per-read limit: their records follow the group's
+            int rc = enumerate_long_reads(h, B, out, n_long, n);
+            if (rc) return rc;
+        }
+        const u64 *recs = out.recs;
+        u64 *sorted = h->region_sort ? (u64 *)h->d_send.p + base[g] * RW : nullptr;
+        bool fell_back = false;
+        if (n > ccap[g]) {
+            if (g == 0) return BRISK_OK;  // nothing applied yet: the plain path takes the whole batch
+            // the group's region was too small: enumerate its chunks again the plain way, into d_recs from its start,
+            // once the earlier groups' kernels are done with it; the group is then stored on the handle's stream, which
+            // orders it before everything the later groups do to these buffers
+            CK(cudaStreamSynchronize(side));
+            side_busy = false;
+            uint64_t n_occ = 0;
+            int rc = enumerate_batch(h, B, false, n, n_occ, cut[g], cut[g + 1]);
+            if (rc) return rc;
+            if (h->region_sort) CK(h->d_send.ensure((std::max(n, base[ng]) + 1) * RW * sizeof(uint64_t)));
+            recs = (const u64 *)h->d_recs.p;
+            sorted = h->region_sort ? (u64 *)h->d_send.p : nullptr;
+            fell_back = true;
+        }
+        if (last || fell_back) {
+            if (last) {
+                CK(cudaEventRecord(h->ev[2], h->stream));
+                CK(cudaEventRecord(h->ev[3], h->stream));
+            }
+            if (side_busy) CK(cudaStreamWaitEvent(h->stream, h->ov_ev[1], 0));
+            side_busy = false;
+            int rc = store_group(recs, n, sorted, nullptr, 0);
+            if (rc) return rc;
+        } else {
+            CK(cudaEventRecord(h->ov_ev[0], h->stream));
+            CK(cudaStreamWaitEvent(side, h->ov_ev[0], 0));
+            int rc = store_group(recs, n, sorted, side, ctas_env);
+            if (rc) return rc;
+            CK(cudaEventRecord(h->ov_ev[1], side));
+            side_busy = true;
+        }
+        done = true;  // from here on part of the batch is in the store
+    }
+    return BRISK_OK;
+}
+
 // shared driver of count / insert / get over reads
 static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets, uint64_t n_reads, int mode,
                      uint64_t *slots, uint8_t *flags, void *data_out, uint64_t *agg_out = nullptr) {
@@ -1246,13 +1401,17 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         return BRISK_OK;
     };
     DevBuf back_slots, back_flags, back_data;
-    // (Running the store kernel chunk by chunk as the host copies arrive was measured twice: slower.  Eight small
-    // launches lose the region order's locality (each chunk walks the whole table) and the enumerate launches lose
-    // to wave quantisation; the call went from 8.4-8.8 ms to 9.1-9.9 ms.  Instead count / insert calls return once
-    // their input is consumed, and the NEXT call's host->device copy overlaps this call's store kernel.  Storing the
-    // first half of the chunks while the second half is on its way was measured too: the count call grows by what the
-    // next call saves, 15.6 -> 16.9 ms per step: the step is bound by its kernels, not by the copies.)
-    {
+    // Host input: count / insert calls return once their input is consumed, and the NEXT call's host->device copy
+    // overlaps this call's last store kernel; within a call the records of the first chunks are stored while the last
+    // chunks are still arriving (run_reads_overlapped: two groups; finer cuts were measured and lose to the per-group
+    // costs and to the contention with the enumeration, profiles/r2_e2e_overlap.md).
+    bool overlapped = false;
+    if (!sharded && !with_occ && B.chunk_events) {
+        O.agg = agg_out ? h->counters + 5 : nullptr;
+        rc = run_reads_overlapped(h, B, mode, O, overlapped);
+        if (rc) return rc;
+    }
+    if (!overlapped) {
         Exchange X;
         bool exchanged = false;
         if (sharded && !with_occ && !(h->flags & BRISK_F_SERIAL_EXCHANGE)) {
