@@ -77,6 +77,7 @@ struct brisk_handle {
     cudaEvent_t offsets_ev = nullptr;
     cudaStream_t store_stream = nullptr;  // run_reads_overlapped: the store kernel of a batch's first chunks (low priority)
     cudaEvent_t ov_ev[2] = {};            // [0] the handle's stream is ready for that kernel, [1] the kernel is done
+    bool pending_on_side = false;         // the pending store kernel runs on store_stream (its records are in d_send)
     bool pending_settle = false;  // a count / insert call left its store kernel running: settle() before the table is used again
     bool timing_dirty = false;    // stage times of the last call not read back yet
     float last_ms[5] = {0, 0, 0, 0, 0};
@@ -354,6 +355,7 @@ extern "C" int brisk_destroy(brisk_t *h) {
     if (!h) return BRISK_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->store_stream) cudaStreamSynchronize(h->store_stream);
     DevBuf *bufs[] = {&h->d_bases, &h->d_offsets, &h->d_packed, &h->d_recs, &h->d_rec_occ, &h->d_kmer_base, &h->d_cnt,
                       &h->d_out_slots, &h->d_out_flags, &h->d_out_data, &h->d_kmers, &h->d_cub, &h->d_long, &h->d_send, &h->d_send_occ,
                       &h->d_recv, &h->d_recv_occ, &h->d_occ_off, &h->d_ret_slots, &h->d_ret_flags, &h->d_ret_data,
@@ -482,7 +484,7 @@ static int pack_chunk(brisk_handle *h, const ReadBatch &B, size_t c) {
     const uint64_t r0 = B.chunk_first[c], r1 = B.chunk_first[c + 1];
     if (B.chunk_events) CK(cudaStreamWaitEvent(h->stream, h->chunk_ev[c], 0));
     if (r1 > r0) {
-        unsigned blocks = (unsigned)((r1 - r0 + 7) / 8);
+        unsigned blocks = (unsigned)((r1 - r0 + PACK_READS_PER_CTA - 1) / PACK_READS_PER_CTA);
         pack_reads_kernel<<<blocks, 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
         CK(cudaGetLastError());
         h->last_launches++;
@@ -957,7 +959,7 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
     const bool two_streams = !B.chunk_events && nc > 1 && nc <= 3 && xmode >= 2 && (xmode == 2 || c.aux_ordered);
     if (two_streams) {  // the whole batch is packed first (its bases are resident), then the chunks only enumerate
         if (B.n_reads) {
-            pack_reads_kernel<<<(unsigned)((B.n_reads + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, 0, B.n_reads, B.d_packed);
+            pack_reads_kernel<<<(unsigned)((B.n_reads + PACK_READS_PER_CTA - 1) / PACK_READS_PER_CTA), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, 0, B.n_reads, B.d_packed);
             CK(cudaGetLastError());
             h->last_launches++;
         }
@@ -976,7 +978,7 @@ static int exchange_pipelined(brisk_handle *h, const ReadBatch &B, int local_sta
         if (B.chunk_events) CK(cudaStreamWaitEvent(h->stream, h->chunk_ev[ci], 0));
         if (r1 > r0) {
             if (!two_streams) {
-                pack_reads_kernel<<<(unsigned)((r1 - r0 + 7) / 8), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
+                pack_reads_kernel<<<(unsigned)((r1 - r0 + PACK_READS_PER_CTA - 1) / PACK_READS_PER_CTA), 256, 0, h->stream>>>(B.d_bases, B.d_offsets, r0, r1, B.d_packed);
                 CK(cudaGetLastError());
                 h->last_launches++;
             }
@@ -1184,6 +1186,10 @@ static int settle(brisk_handle *h) {
 static int settle_pending(brisk_handle *h) {
     if (!h->pending_settle) return BRISK_OK;
     h->pending_settle = false;
+    if (h->pending_on_side) {  // the store kernel was left running on the side stream: the handle's stream joins it
+        h->pending_on_side = false;
+        CK(cudaStreamWaitEvent(h->stream, h->ov_ev[1], 0));
+    }
     return settle(h);
 }
 #define SETTLE_PENDING(h) do { int prc_ = settle_pending(h); if (prc_) return prc_; } while (0)
@@ -1204,6 +1210,14 @@ static void finish_timing(brisk_handle *h) {
 // of the last chunk and the store kernel over the last group only.  Each group enumerates into its own region of
 // d_recs and is put in table-region order on its own (d_send, same regions).  done = false: nothing has been applied
 // (the first group's region was too small) and the caller runs the plain path.
+static int ensure_side_stream(brisk_handle *h) {
+    if (h->store_stream) return BRISK_OK;
+    int lo_p = 0, hi_p = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
+    CK(cudaStreamCreateWithPriority(&h->store_stream, cudaStreamNonBlocking, lo_p));
+    for (int i = 0; i < 2; i++) CK(cudaEventCreateWithFlags(&h->ov_ev[i], cudaEventDisableTiming));
+    return BRISK_OK;
+}
 static std::vector<size_t> overlap_cuts(const char *env_name, const char *dflt) {
     const char *e = getenv(env_name);
     std::vector<size_t> v;
@@ -1230,11 +1244,9 @@ static int run_reads_overlapped(brisk_handle *h, const ReadBatch &B, int mode, O
     const int ng = (int)cut.size() - 1;
     if (ng < 2 || nc < 4) return BRISK_OK;
     const int RW = h->P.rec_words;
-    if (!h->store_stream) {
-        int lo_p = 0, hi_p = 0;
-        CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
-        CK(cudaStreamCreateWithPriority(&h->store_stream, cudaStreamNonBlocking, lo_p));
-        for (int i = 0; i < 2; i++) CK(cudaEventCreateWithFlags(&h->ov_ev[i], cudaEventDisableTiming));
+    {
+        int src = ensure_side_stream(h);
+        if (src) return src;
     }
     cudaStream_t side = stream_env ? h->store_stream : h->stream;
     if (mode != MODE_GET) {  // room for the whole batch before its first store kernel (a rehash runs on the handle's stream)
@@ -1362,7 +1374,13 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
     // after staging: this call's host->device copies run while the previous store kernel finishes.  On a sharded index a
     // deferred failure (store full) must not make this rank leave before the collectives of the call: it is carried
     // into the exchange, where every rank learns of it
-    const int settle_rc = settle_pending(h);
+    // Device-resident input on an unsharded index: the pending store kernel of the previous call (memory-bound, on the
+    // side stream, its records in d_send) and this call's pack + enumerate (ALU-bound, on the handle's stream, into
+    // d_recs) share no buffer, so the previous call is only settled once this call's records exist
+    static const int async_store = getenv("BRISK_ASYNC_STORE") ? atoi(getenv("BRISK_ASYNC_STORE")) : 0;
+    static const int async_ctas = getenv("BRISK_ASYNC_CTAS") ? atoi(getenv("BRISK_ASYNC_CTAS")) : 2;
+    const bool late_settle = !sharded && h->pending_settle && h->pending_on_side && !B.chunk_events;
+    const int settle_rc = late_settle ? BRISK_OK : settle_pending(h);
     if (settle_rc && !sharded) return settle_rc;
     uint64_t n_recs = 0, n_occ = 0;
     OccOut O;
@@ -1424,6 +1442,10 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         if (!exchanged) {
             rc = enumerate_batch(h, B, with_occ, n_recs, n_occ);
             if (rc) return rc;
+            if (late_settle) {
+                rc = settle_pending(h);
+                if (rc) return rc;
+            }
             CK(cudaEventRecord(h->ev[2], h->stream));
             X.recs = (const u64 *)h->d_recs.p;
             X.n = n_recs;
@@ -1460,7 +1482,21 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
             if (flags) { CK(h->d_ret_flags.ensure(n_ret + 1)); O.flags = (unsigned char *)h->d_ret_flags.p; }
             if (data_out) { CK(h->d_ret_data.ensure((n_ret + 1) * h->data_size)); O.data = (unsigned char *)h->d_ret_data.p; }
         }
-        CK(launch_records(h, mode, X.recs, X.n, O));
+        const bool leave_pending = mode != MODE_GET && !with_occ && !(h->flags & BRISK_F_SYNC_INSERT);
+        const bool on_side = async_store && leave_pending && !sharded && !B.chunk_events && X.n &&
+                             X.recs == (const u64 *)h->d_send.p;  // (records in d_recs would be overwritten by the next enumeration)
+        if (on_side) {
+            rc = ensure_side_stream(h);
+            if (rc) return rc;
+            CK(cudaEventRecord(h->ov_ev[0], h->stream));
+            CK(cudaStreamWaitEvent(h->store_stream, h->ov_ev[0], 0));
+            CK(launch_records(h, mode, X.recs, X.n, O, h->store_stream, async_ctas));
+            CK(cudaEventRecord(h->ov_ev[1], h->store_stream));
+            CK(cudaEventRecord(h->ev[4], h->store_stream));
+            h->pending_on_side = true;
+        } else {
+            CK(launch_records(h, mode, X.recs, X.n, O));
+        }
         if (X.n) h->last_launches++;
         if (sharded && with_occ) {
             rc = return_results(h, X, n_recs, slots != nullptr, flags != nullptr, data_out != nullptr, back_slots, back_flags, back_data,
@@ -1470,7 +1506,7 @@ static int run_reads(brisk_handle *h, const char *bases, const uint64_t *offsets
         if (sharded && agg_out)  // every rank gets the totals of the whole query batch
             NCK(g_nccl.AllReduce(h->counters + 5, h->counters + 5, 2, ncclUint64, ncclSum, h->comm->comm, h->stream));
     }
-    CK(cudaEventRecord(h->ev[4], h->stream));
+    if (!h->pending_on_side) CK(cudaEventRecord(h->ev[4], h->stream));
     if (slots && !s_dev) CK(cudaMemcpyAsync(slots, o_slots, n_occ * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     if (flags && !f_dev) CK(cudaMemcpyAsync(flags, o_flags, n_occ, cudaMemcpyDeviceToHost, h->stream));
     if (data_out && !d_dev) CK(cudaMemcpyAsync(data_out, o_data, n_occ * h->data_size, cudaMemcpyDeviceToHost, h->stream));

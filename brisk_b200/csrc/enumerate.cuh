@@ -24,33 +24,74 @@
 #define ENUM_SYNC_STEPS 32
 
 // ---------------------------------------------------------------------------------------------
+// 2 bits per base, first base on top: the 8 bases in the bytes of x (byte 0 first) -> 16 bits
+__device__ __forceinline__ u32 pack8(u64 x) {
+    const u32 xl = (u32)x, xh = (u32)(x >> 32);
+    u64 t = ((u64)__byte_perm(xl, 0, 0x0123) << 32) | (u64)__byte_perm(xh, 0, 0x0123);  // byte 0 on top
+    t = (t >> 1) & 0x0303030303030303ull;
+    t = (t | (t >> 6)) & 0x000F000F000F000Full;
+    t = (t | (t >> 12)) & 0x000000FF000000FFull;
+    return (u32)((t | (t >> 24)) & 0xFFFFull);
+}
+
+#define PACK_READS_PER_WARP 4
+#define PACK_READS_PER_CTA (8 * PACK_READS_PER_WARP)  // 256 threads
+// A warp packs PACK_READS_PER_WARP consecutive reads.  The kernel is bound by memory round trips (offsets, then bases),
+// so the offsets of the warp's reads come with one request and the first 256 bases of all of them are requested
+// before any is used.  Lane l fetches bases [8l, 8l+8) of a 256-base block as the (at most) two ALIGNED 8-byte words
+// that hold them (a read starts at any byte; only words with at least one byte of the read are touched).
 __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__restrict__ bases,
                                                          const u64 *__restrict__ offsets, u64 read0, u64 read_end,
                                                          u64 *__restrict__ packed) {
+    constexpr int R = PACK_READS_PER_WARP;
     const int lane = threadIdx.x & 31;
-    const u64 r = read0 + (u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);  // reads [read0, read_end) of the batch
-    if (r >= read_end) return;
-    const u64 beg = offsets[r], end = offsets[r + 1];
-    const u64 len = end - beg;
-    u64 *out = packed + packed_start(beg, r);
-    const unsigned char *src = bases + beg;
-    // a warp packs 256 bases (8 words) per iteration, lane -> 8 consecutive bases: the eight byte loads of a lane are
-    // independent, so a read of up to 256 bases costs ONE memory round trip (the kernel is latency-bound: two
-    // dependent offset loads, then the bases)
-    for (u64 base0 = 0; base0 < len; base0 += 256) {
-        const u64 p = base0 + 8 * (u64)lane;
-        u32 c[8];
+    const u64 r0 = read0 + ((u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;  // reads [read0, read_end) of the batch
+    if (r0 >= read_end) return;
+    const int nr = (int)(read_end - r0 < (u64)R ? read_end - r0 : (u64)R);
+    const u64 my_off = lane <= nr ? offsets[r0 + lane] : 0;
+    u64 beg[R], len[R], lo[R], hi[R];
+    unsigned sh[R];
 #pragma unroll
-        for (int j = 0; j < 8; j++) c[j] = (p + j < len) ? (u32)src[p + j] : 0u;
-        u32 v = 0;
-#pragma unroll
-        for (int j = 0; j < 8; j++) v = (v << 2) | ((c[j] >> 1) & 3u);
-        // lane g*4+i holds bases [32g+8i, 32g+8i+8): place its 16 bits at bits (3-i)*16 of word g
-        u64 x = (u64)v << (16 * (3 - (lane & 3)));
-        x |= __shfl_xor_sync(0xffffffffu, x, 1);
-        x |= __shfl_xor_sync(0xffffffffu, x, 2);
-        if ((lane & 3) == 0 && base0 + 32 * (u64)(lane >> 2) < len) out[(base0 >> 5) + (lane >> 2)] = x;
+    for (int i = 0; i < R; i++) {
+        beg[i] = __shfl_sync(0xffffffffu, my_off, i);
+        const u64 end = __shfl_sync(0xffffffffu, my_off, i + 1);
+        len[i] = i < nr ? end - beg[i] : 0;
     }
+    auto fetch = [&](int i, u64 base0) {
+        const unsigned char *src = bases + beg[i];
+        sh[i] = (unsigned)((uintptr_t)src & 7u) * 8u;
+        const u64 *asrc = reinterpret_cast<const u64 *>((uintptr_t)src & ~(uintptr_t)7);
+        const u64 p = base0 + 8 * (u64)lane, wi = p >> 3;
+        lo[i] = 0; hi[i] = 0;
+        if (p < len[i]) {
+            const u64 last_word = (((uintptr_t)src & 7u) + len[i] - 1) >> 3;  // the word with the read's last base
+            lo[i] = __ldg(asrc + wi);
+            if (sh[i] && wi + 1 <= last_word) hi[i] = __ldg(asrc + wi + 1);
+        }
+    };
+    auto emit = [&](int i, u64 base0) {
+        const u64 p = base0 + 8 * (u64)lane;
+        u64 x = sh[i] ? (lo[i] >> sh[i]) | (hi[i] << (64 - sh[i])) : lo[i];  // byte j = base p + j
+        const u64 left = p < len[i] ? len[i] - p : 0;
+        if (left < 8) x &= left ? (~0ull >> (64 - 8 * left)) : 0ull;
+        // lane g*4+j holds bases [32g+8j, 32g+8j+8): its 16 bits go to bits (3-j)*16 of word g
+        u64 w = (u64)pack8(x) << (16 * (3 - (lane & 3)));
+        w |= __shfl_xor_sync(0xffffffffu, w, 1);
+        w |= __shfl_xor_sync(0xffffffffu, w, 2);
+        if ((lane & 3) == 0 && base0 + 32 * (u64)(lane >> 2) < len[i])
+            packed[packed_start(beg[i], r0 + i) + (base0 >> 5) + (lane >> 2)] = w;
+    };
+#pragma unroll
+    for (int i = 0; i < R; i++) fetch(i, 0);
+#pragma unroll
+    for (int i = 0; i < R; i++) emit(i, 0);
+    // reads beyond 256 bases: block after block
+#pragma unroll
+    for (int i = 0; i < R; i++)
+        for (u64 base0 = 256; base0 < len[i]; base0 += 256) {
+            fetch(i, base0);
+            emit(i, base0);
+        }
 }
 
 // ---------------------------------------------------------------------------------------------

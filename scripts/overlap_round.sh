@@ -1,19 +1,15 @@
 #!/bin/bash
-# A/B of the host-input overlap (run_reads_overlapped) under the development switches
 mkdir -p gpurun_out
-while read -r c g t; do
-  TAG="count=$c get=$g ctas=$t" BRISK_OVERLAP_COUNT=$c BRISK_OVERLAP_GET=$g BRISK_OVERLAP_CTAS=$t python scripts/e2e_timeline.py 2>&1 | tail -1
-done <<'LIST' | tee gpurun_out/ov_timeline4.txt
-3 3 2
-4 3 2
-5 3 2
-2,5 3 2
-3,6 3 2
-3 2 2
-3 4 2
-3 2,4 2
-4 4 2
-4 2 2
-3,6 2 3
-3 3 3
+while read -r a c m; do
+  TAG="async=$a ctas=$c" MODE=$m BRISK_ASYNC_STORE=$a BRISK_ASYNC_CTAS=$c python scripts/dev_timeline.py 2>&1 | tail -1
+done <<'LIST' | tee gpurun_out/async_store.txt
+0 0 count+query
+1 0 count+query
+1 1 count+query
+1 2 count+query
+1 3 count+query
+0 0 count
+1 0 count
+1 2 count
+1 3 count
 LIST
