@@ -431,9 +431,22 @@ def run_ours(args):
                 "share_of_step": launches_per_step * ms / step_ms, "note": note}
 
     r_enum = roof("pack_reads_kernel + enumerate_kernel<%d,%d> (stage A+B of SURVEY.md 8(d))" % (K, M), ab_bytes, pack_ms + enum_ms, 2,
-                  "bound by the integer ALU pipe, not by HBM (ncu: profiles/r2_summary.md); the bytes are the stage's ASCII input "
+                  "bound by the integer ALU pipe (79.5 %% of its peak), not by HBM (ncu: profiles/r2_final_kernels.json); the bytes are the stage's ASCII input "
                   "(read by pack_reads_kernel) plus the packed records written; pack %.3f ms + enumerate %.3f ms per launch; "
-                  "traffic: see the ncu capture named in profiles/r2_summary.md (not re-measured by this run)" % (pack_ms, enum_ms))
+                  "traffic: see traffic_source" % (pack_ms, enum_ms))
+    # DRAM traffic of the two kernels from the committed ncu --set full captures of this command (cfg 3 at full size):
+    # only for the workload they were taken on
+    kfile = os.path.join(ROOT, "profiles", "r2_final_kernels.json")
+    if W.name == "cfg3" and not args.genome and n_reads == BATCH_READS and os.path.exists(kfile):
+        kk = json.load(open(kfile))["kernels"]
+        e, pk = kk["enumerate_kernel<63,21,4>"], kk["pack_reads_kernel"]
+        r_enum["traffic"] = e["dram_bytes_read"] + e["dram_bytes_write"] + pk["dram_bytes_read"] + pk["dram_bytes_write"]
+        r_enum["traffic_source"] = ("ncu --set full captures of `bench.py --steps 2 --warmup 3`, one launch each, "
+                                    "profiles/r2_final_kernels.json (+ r2_final_enumerate_full.csv, r2_final_pack_full.csv): "
+                                    "enumerate_kernel %.1f MB (tree 6e2412a, kernel unchanged since) + pack_reads_kernel %.1f MB "
+                                    "(captured on 6e2412a, before the kernel's last rewrite: a streaming kernel, ASCII in, 2-bit "
+                                    "words out); not re-measured by this run" %
+                                    ((e["dram_bytes_read"] + e["dram_bytes_write"]) / 1e6, (pk["dram_bytes_read"] + pk["dram_bytes_write"]) / 1e6))
     r_ins = roof("records_kernel<COUNT> (insert/count)", ins_bytes, ins_ms, 1,
                  "one 32-byte slot sector read per occurrence plus the count word of the side array (red.add, one sector per "
                  "superkmer); the 18 B per occurrence of SURVEY.md 8(d) assumes byte-granular access")

@@ -24,74 +24,52 @@
 #define ENUM_SYNC_STEPS 32
 
 // ---------------------------------------------------------------------------------------------
-// 2 bits per base, first base on top: the 8 bases in the bytes of x (byte 0 first) -> 16 bits
-__device__ __forceinline__ u32 pack8(u64 x) {
-    const u32 xl = (u32)x, xh = (u32)(x >> 32);
-    u64 t = ((u64)__byte_perm(xl, 0, 0x0123) << 32) | (u64)__byte_perm(xh, 0, 0x0123);  // byte 0 on top
-    t = (t >> 1) & 0x0303030303030303ull;
-    t = (t | (t >> 6)) & 0x000F000F000F000Full;
-    t = (t | (t >> 12)) & 0x000000FF000000FFull;
-    return (u32)((t | (t >> 24)) & 0xFFFFull);
+// 2 bits per base, first base on top: the 4 bases in the bytes of h (byte 0 first) -> 8 bits
+__device__ __forceinline__ u32 pack4(u32 h) {
+    u32 t = (__byte_perm(h, 0, 0x0123) >> 1) & 0x03030303u;  // byte 0 on top, (c >> 1) & 3 (Kmers.cpp:442-444)
+    t = (t | (t >> 6)) & 0x000F000Fu;
+    return (t | (t >> 12)) & 0xFFu;
 }
+__device__ __forceinline__ u32 pack8(u64 x) { return (pack4((u32)x) << 8) | pack4((u32)(x >> 32)); }
 
 #define PACK_READS_PER_WARP 4
 #define PACK_READS_PER_CTA (8 * PACK_READS_PER_WARP)  // 256 threads
-// A warp packs PACK_READS_PER_WARP consecutive reads.  The kernel is bound by memory round trips (offsets, then bases),
-// so the offsets of the warp's reads come with one request and the first 256 bases of all of them are requested
-// before any is used.  Lane l fetches bases [8l, 8l+8) of a 256-base block as the (at most) two ALIGNED 8-byte words
-// that hold them (a read starts at any byte; only words with at least one byte of the read are touched).
+// A warp packs PACK_READS_PER_WARP consecutive reads: 8 lanes per read, one lane per output word (32 bases), so a read
+// of up to 256 bases takes one pass and no exchange between lanes.  The offsets of the warp's reads come with one
+// request.  A lane fetches its 32 bases as the (at most five) ALIGNED 8-byte words that hold them (a read starts at
+// any byte; only words with at least one byte of the read are touched) and funnel-shifts them into place.
 __global__ void __launch_bounds__(256) pack_reads_kernel(const unsigned char *__restrict__ bases,
                                                          const u64 *__restrict__ offsets, u64 read0, u64 read_end,
                                                          u64 *__restrict__ packed) {
     constexpr int R = PACK_READS_PER_WARP;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, sub = lane >> 3, wl = lane & 7;
     const u64 r0 = read0 + ((u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;  // reads [read0, read_end) of the batch
     if (r0 >= read_end) return;
     const int nr = (int)(read_end - r0 < (u64)R ? read_end - r0 : (u64)R);
     const u64 my_off = lane <= nr ? offsets[r0 + lane] : 0;
-    u64 beg[R], len[R], lo[R], hi[R];
-    unsigned sh[R];
+    const u64 beg = __shfl_sync(0xffffffffu, my_off, sub), end = __shfl_sync(0xffffffffu, my_off, sub + 1);
+    if (sub >= nr) return;
+    const u64 len = end - beg, n_words = (len + 31) >> 5;
+    const unsigned char *src = bases + beg;
+    const unsigned mis = (unsigned)((uintptr_t)src & 7u), sh = mis * 8u;
+    const u64 *asrc = reinterpret_cast<const u64 *>((uintptr_t)src - mis);
+    const u64 last_word = len ? (mis + len - 1) >> 3 : 0;  // the aligned word (from asrc) with the read's last base
+    u64 *out = packed + packed_start(beg, r0 + sub);
+    for (u64 w = wl; w < n_words; w += 8) {
+        const u64 wi = 4 * w;  // bases [32w, 32w + 32) start in aligned word wi at bit sh
+        u64 q[5];
 #pragma unroll
-    for (int i = 0; i < R; i++) {
-        beg[i] = __shfl_sync(0xffffffffu, my_off, i);
-        const u64 end = __shfl_sync(0xffffffffu, my_off, i + 1);
-        len[i] = i < nr ? end - beg[i] : 0;
+        for (int j = 0; j < 5; j++) q[j] = (wi + j <= last_word && (j < 4 || sh)) ? __ldg(asrc + wi + j) : 0ull;
+        const u64 left = len - 32 * w;  // >= 1 bases from here to the read's end
+        u64 word = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            u64 x = sh ? (q[j] >> sh) | (q[j + 1] << (64 - sh)) : q[j];  // byte i = base 32w + 8j + i
+            if (left < 8u * (j + 1)) x = left > 8u * j ? x & (~0ull >> (64 - 8 * (left - 8u * j))) : 0ull;
+            word = (word << 16) | pack8(x);
+        }
+        out[w] = word;
     }
-    auto fetch = [&](int i, u64 base0) {
-        const unsigned char *src = bases + beg[i];
-        sh[i] = (unsigned)((uintptr_t)src & 7u) * 8u;
-        const u64 *asrc = reinterpret_cast<const u64 *>((uintptr_t)src & ~(uintptr_t)7);
-        const u64 p = base0 + 8 * (u64)lane, wi = p >> 3;
-        lo[i] = 0; hi[i] = 0;
-        if (p < len[i]) {
-            const u64 last_word = (((uintptr_t)src & 7u) + len[i] - 1) >> 3;  // the word with the read's last base
-            lo[i] = __ldg(asrc + wi);
-            if (sh[i] && wi + 1 <= last_word) hi[i] = __ldg(asrc + wi + 1);
-        }
-    };
-    auto emit = [&](int i, u64 base0) {
-        const u64 p = base0 + 8 * (u64)lane;
-        u64 x = sh[i] ? (lo[i] >> sh[i]) | (hi[i] << (64 - sh[i])) : lo[i];  // byte j = base p + j
-        const u64 left = p < len[i] ? len[i] - p : 0;
-        if (left < 8) x &= left ? (~0ull >> (64 - 8 * left)) : 0ull;
-        // lane g*4+j holds bases [32g+8j, 32g+8j+8): its 16 bits go to bits (3-j)*16 of word g
-        u64 w = (u64)pack8(x) << (16 * (3 - (lane & 3)));
-        w |= __shfl_xor_sync(0xffffffffu, w, 1);
-        w |= __shfl_xor_sync(0xffffffffu, w, 2);
-        if ((lane & 3) == 0 && base0 + 32 * (u64)(lane >> 2) < len[i])
-            packed[packed_start(beg[i], r0 + i) + (base0 >> 5) + (lane >> 2)] = w;
-    };
-#pragma unroll
-    for (int i = 0; i < R; i++) fetch(i, 0);
-#pragma unroll
-    for (int i = 0; i < R; i++) emit(i, 0);
-    // reads beyond 256 bases: block after block
-#pragma unroll
-    for (int i = 0; i < R; i++)
-        for (u64 base0 = 256; base0 < len[i]; base0 += 256) {
-            fetch(i, base0);
-            emit(i, base0);
-        }
 }
 
 // ---------------------------------------------------------------------------------------------

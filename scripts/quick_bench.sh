@@ -1,7 +1,7 @@
 #!/bin/bash
 # one short bench line (no CPU leg, no independent index) + the stage times
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_parity.py -x -q -k "golden or enumerat" 2>&1 | tail -2
+python -m pytest tests/test_gpu_parity.py tests/test_gpu_long_reads.py tests/test_gpu_overlap.py -x -q 2>&1 | tail -2
 python bench.py --no-cpu-baseline --no-parity > gpurun_out/quick.json 2>gpurun_out/quick.err
 python - <<PY
 import json
