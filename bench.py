@@ -20,7 +20,8 @@ Every run checks itself (`parity_check` in the line): each query step must find 
 of the stored counts must equal the occurrences inserted, and the checksum of the stored set (brisk_checksum, summed
 over the ranks) must equal the checksum of an independent index over the same reads — at N = 1 an index enumerated by
 the run-time-(k, m) kernel with the LITERAL decycling sums, at N > 1 an unsharded index on rank 0 (so the NCCL exchange
-is witnessed at every N the driver runs).
+is witnessed at every N the driver runs).  The host-buffer (e2e) arm counts the same batches in the same order: its final
+store must have the device arm's checksum, shard by shard (`e2e_store_equals_device_arm`).
 """
 import argparse
 import json
@@ -398,7 +399,18 @@ def run_ours(args):
 
     ms_e2e, acc_e2e = float("nan"), None
     if not args.skip_e2e:
-        ms_e2e, acc_e2e, _, _, _ = timed(host_batches, offs_host, stage_times=False)
+        ms_e2e, acc_e2e, _, _, idx_e2e = timed(host_batches, offs_host, stage_times=False, keep=True)
+        # the host-buffer arm counts the same batches in the same order: its store must be the device arm's, shard by shard
+        cs_e2e = idx_e2e.checksum()
+        idx_e2e.close()
+        same = int(cs_e2e == cs and acc_e2e["query_ok"] == acc_e2e["query_steps"])
+        if world > 1:
+            t_same = torch.tensor([same], device="cuda")
+            dist.all_reduce(t_same, op=dist.ReduceOp.MIN)
+            same = int(t_same.item())
+        parity["e2e_store_equals_device_arm"] = bool(same)
+        if "ok" in parity:
+            parity["ok"] = bool(parity["ok"] and same)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
