@@ -83,3 +83,18 @@ def test_create_flags_match_the_header():
     flags = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define BRISK_F_(\w+)\s+(\d+)u", text)}
     assert flags == {"MANAGED": B.F_MANAGED, "LITERAL_DECYCLE": B.F_LITERAL_DECYCLE, "SYNC_INSERT": B.F_SYNC_INSERT,
                      "GENERIC_ENUM": B.F_GENERIC_ENUM, "SERIAL_EXCHANGE": B.F_SERIAL_EXCHANGE}
+
+
+def test_noalloc_entry_point_checks_its_arguments_first():
+    # brisk_checksum_kmers_noalloc (no counterpart in the reference): the size limit of the static scratch and the null
+    # checks come before anything touches the device, so they can be seen without one
+    import ctypes as C
+    from brisk_b200 import _capi
+    lib = _capi.load()
+    out = (C.c_uint64 * 3)()
+    assert lib.brisk_checksum_kmers_noalloc(None, None, 1, out, None) == -1
+    assert lib.brisk_checksum_kmers_noalloc(None, None, 0, None, None) == -1
+    buf = (C.c_uint8 * 24)()
+    assert lib.brisk_checksum_kmers_noalloc(buf, buf, (1 << 26) + 1, out, None) == -3
+    msg = lib.brisk_last_error().decode()
+    assert "limit" in msg and str(1 << 26) in msg

@@ -46,3 +46,17 @@ def test_enumerate_kernel_keeps_its_state_in_registers(fun):
     # the rolled decycling class is fixed-point integer arithmetic: the steady state holds no double
     # multiply-add; double additions remain in the literal fallback (DecyclingSet::memDouble as written)
     assert "IMAD.HI" in sass and "DFMA" not in sass
+
+
+def test_pack_kernel_fetches_aligned_words_not_bytes():
+    # a lane fetches its 32 bases as aligned 8-byte words (the byte-load version was bound by the ALU pipe)
+    sass = _sass("_Z17pack_reads_kernelPKhPKyyyPy")
+    assert "pack_reads_kernel" in sass
+    assert re.search(r"LDG\.E\.64", sass), "no 64-bit load in pack_reads_kernel"
+    assert not re.search(r"LDG\.E\.U8", sass), "byte loads in pack_reads_kernel"
+    assert not re.search(r"\b(LDL|STL)\b", sass), "local memory in pack_reads_kernel"
+
+
+def test_noalloc_checksum_kernel_is_in_the_library():
+    sass = _sass("_Z29checksum_kmers_noalloc_kernelPKyPKhyPyS3_")
+    assert "checksum_kmers_noalloc_kernel" in sass and "ATOMG" in sass  # the ticket that elects the last CTA
